@@ -1,0 +1,120 @@
+/* b200head.h - C ABI of the B200-native MIL-NCE / soft-DTW loss head.
+ *
+ * The reference (KoDohwan/MIL-NCE_HowTo100M) is pure Python and has no FFI
+ * layer; its boundary for this path is the Python module API.  Each entry
+ * point below is what a binding for that API calls, and cites the reference
+ * code it replaces.  The Python mirror of the reference modules lives in
+ * mil-nce_howto100m_b200/{loss,soft_dtw_cuda,utils}.py and calls these through
+ * ctypes; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name starts with host_;
+ *     the caller allocates everything, the library allocates no device memory;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*), with
+ *     no host synchronisation inside any call;
+ *   - tensors are dense row-major; return value 0 = ok, negative = error and
+ *     b200head_last_error() (thread-local) explains it;
+ *   - kernels are compiled for sm_100a only; on any other device the calls
+ *     fail with B200HEAD_ERR_DEVICE.  There is no CPU fallback.
+ */
+#ifndef B200HEAD_H
+#define B200HEAD_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200HEAD_OK 0
+#define B200HEAD_ERR_ARG (-1)     /* bad argument / unsupported shape            */
+#define B200HEAD_ERR_CUDA (-2)    /* a CUDA runtime or driver call failed        */
+#define B200HEAD_ERR_DEVICE (-3)  /* current device is not compute capability 10 */
+#define B200HEAD_ERR_WS (-4)      /* workspace too small or misaligned           */
+
+#define B200HEAD_F32 0
+#define B200HEAD_BF16 1
+
+#define B200HEAD_DIST_COSINE 0        /* exp(1 - cos)   soft_dtw_cuda.py:338-348 */
+#define B200HEAD_DIST_NEGATIVE_DOT 1  /* -<x,y>         soft_dtw_cuda.py:351-363 */
+#define B200HEAD_DIST_EUCLIDEAN 2     /* exp(||x-y||)   soft_dtw_cuda.py:326-335 */
+
+/* Message for the last failing call on this host thread ("" if none). */
+const char *b200head_last_error(void);
+/* ABI version (bumped when a signature changes). */
+int b200head_version(void);
+
+/* ------------------------------------------------------------------------
+ * MIL-NCE loss: replaces MILNCELoss.forward (reference loss.py:10-18) and
+ * its autograd backward.  video is (B, D), text is (B*K, D), sample-major
+ * (row j*K+k = candidate k of sample j; reference train.py:212-213).
+ *
+ * The range [i0, i0+n) selects the samples this call owns.  n == B is the
+ * single-GPU case.  With n < B a rank computes exactly the slice that the
+ * reference's AllGather.backward (utils.py:20-24) would hand back to it:
+ * the caller all-gathers video/text first (replacing utils.py:11-17), calls
+ * forward with its range, all-gathers `den`, then calls backward.
+ * ------------------------------------------------------------------------ */
+
+/* Bytes of scratch needed by milnce_forward/milnce_backward for this shape. */
+size_t milnce_workspace_bytes(int B, int K, int D, int dtype, int n);
+
+/* Forward.  den[B], nom[B]: entries [i0, i0+n) are written.
+ * loss[0] receives sum_{i in range} (den_i - nom_i) / B  (so the sum over
+ * ranks is the reference's mean, loss.py:18).  */
+int milnce_forward(const void *video, const void *text, int B, int K, int D, int dtype,
+                   int i0, int n, float *den, float *nom, float *loss,
+                   void *workspace, size_t workspace_bytes, void *stream);
+
+/* Backward.  den must hold all B entries (all-gathered when sharded); nom
+ * needs entries [i0, i0+n).  grad_loss[0] is d(objective)/d(loss), read on
+ * the device.  Outputs are float32: dvideo (n, D) = rows [i0, i0+n) of
+ * d loss/d video, dtext (n*K, D) = rows [i0*K, (i0+n)*K) of d loss/d text.
+ * reuse_forward_ws != 0 promises that `workspace` is untouched since a
+ * milnce_forward call with the same inputs (skips re-staging the operands). */
+int milnce_backward(const void *video, const void *text, const float *den, const float *nom,
+                    const float *grad_loss, float *dvideo, float *dtext,
+                    int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
+                    void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------
+ * soft-DTW: replaces SoftDTW.forward's distance function + _SoftDTWCUDA
+ * (reference soft_dtw_cuda.py:326-363, 115-175, kernels :34-112).
+ * x is (B, N, d), y is (B, M, d), float32; 1 <= N, M <= 1024.
+ * gamma > 0; bandwidth <= 0 disables Sakoe-Chiba pruning (:60, :104).
+ * ------------------------------------------------------------------------ */
+
+/* Bytes of `aux` that sdtw_forward fills and sdtw_backward consumes. */
+size_t sdtw_aux_bytes(int B, int N, int M, int d);
+
+/* Forward.  out[B] = R[:, N, M].  R (B, N+2, M+2) float32 may be NULL; when
+ * given it is filled exactly like the reference's R (+inf border, R[0,0]=0,
+ * pruned cells +inf; soft_dtw_cuda.py:135-145).  aux (sdtw_aux_bytes, 256-byte
+ * aligned) is always required: it holds the distance matrix and the per-cell
+ * soft-min weights that sdtw_backward consumes.  B <= 65535 per call. */
+int sdtw_forward(const float *x, const float *y, int B, int N, int M, int d,
+                 float gamma, float bandwidth, int dist_kind,
+                 float *R, float *out, void *aux, size_t aux_bytes, void *stream);
+
+/* Backward.  grad_out[B]; dx (B, N, d), dy (B, M, d) float32.  E (B, N, M)
+ * float32 may be NULL; when given it receives d out/d D, the reference's
+ * E[:, 1:N+1, 1:M+1] (soft_dtw_cuda.py:174-175) before the grad_out scale. */
+int sdtw_backward(const float *x, const float *y, const float *grad_out,
+                  int B, int N, int M, int d, float gamma, float bandwidth, int dist_kind,
+                  const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
+                  void *stream);
+
+/* ------------------------------------------------------------------------
+ * Test / diagnostic hooks for the tcgen05 GEMM core (C = alpha * A . B^T with
+ * A (M, Kd) and Bm (N, Kd) float16 row-major, C float32 (M, N)).  No
+ * reference counterpart; used by the GPU tests to validate the TMA / UMMA
+ * descriptors independently of the loss epilogues.
+ * ------------------------------------------------------------------------ */
+int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
+                         int lda, int ldb, int ldc, float alpha, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200HEAD_H */

@@ -1,0 +1,11 @@
+"""B200-native loss head of KoDohwan/MIL-NCE_HowTo100M.
+
+Drop-ins for the reference's ``loss.MILNCELoss``, ``soft_dtw_cuda.SoftDTW`` and
+``utils.AllGather``; all arithmetic is in libb200head.so (csrc/, sm_100a only).
+"""
+from . import _lib
+from .loss import MILNCELoss
+from .soft_dtw_cuda import SoftDTW
+from .utils import AllGather, GatheredMILNCELoss
+
+__all__ = ["MILNCELoss", "SoftDTW", "AllGather", "GatheredMILNCELoss", "_lib"]

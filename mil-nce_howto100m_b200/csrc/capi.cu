@@ -1,0 +1,97 @@
+// Error reporting, device check and TMA descriptor construction for libb200head.
+#include <mutex>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+const char *get_error() { return g_err; }
+
+int check_device() {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        set_error("cudaGetDevice failed: %s (no CUDA device? this library has no CPU path)",
+                  cudaGetErrorString(e));
+        return B200HEAD_ERR_CUDA;
+    }
+    static thread_local int cached_dev = -1, cached_major = 0;
+    if (cached_dev != dev) {
+        int major = 0;
+        e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+        if (e != cudaSuccess) {
+            set_error("cudaDeviceGetAttribute failed: %s", cudaGetErrorString(e));
+            return B200HEAD_ERR_CUDA;
+        }
+        cached_dev = dev;
+        cached_major = major;
+    }
+    if (cached_major != 10) {
+        set_error("device %d has compute capability %d.x; kernels are built for sm_100a only",
+                  dev, cached_major);
+        return B200HEAD_ERR_DEVICE;
+    }
+    return 0;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+                cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    });
+    return fn;
+}
+
+int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t cols,
+                     uint64_t ld, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return B200HEAD_ERR_CUDA;
+    }
+    if (((uintptr_t)base & 15) || ((ld * 2) & 15)) {
+        set_error("TMA operand must be 16-byte aligned with a 16-byte multiple row pitch "
+                  "(base=%p ld=%llu)", base, (unsigned long long)ld);
+        return B200HEAD_ERR_ARG;
+    }
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstr[1] = {ld * 2};
+    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), gdim, gstr,
+                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu ld=%llu)",
+                  (int)r, (unsigned long long)rows, (unsigned long long)cols,
+                  (unsigned long long)ld);
+        return B200HEAD_ERR_CUDA;
+    }
+    return 0;
+}
+
+}  // namespace b200
+
+extern "C" const char *b200head_last_error(void) { return b200::get_error(); }
+extern "C" int b200head_version(void) { return 1; }

@@ -1,0 +1,48 @@
+// Shared host-side helpers for the b200head C-ABI library.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/b200head.h"
+
+namespace b200 {
+
+// Thread-local error message behind b200head_last_error().
+void set_error(const char *fmt, ...);
+const char *get_error();
+
+// 0 if the current device is compute capability 10.x, else an error code.
+int check_device();
+
+// cuTensorMapEncodeTiled resolved at run time through cudaGetDriverEntryPoint so
+// that the library loads (and exports its symbols) on machines without libcuda.
+// Describes a row-major fp16/bf16 matrix `rows x cols` with leading dimension
+// `ld` elements; box = 64 columns (128 bytes, SWIZZLE_128B) x box_rows rows.
+int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t cols,
+                     uint64_t ld, uint32_t box_rows);
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+#define B200_CUDA_OK(expr)                                                                 \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            b200::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),        \
+                            __FILE__, __LINE__);                                           \
+            return B200HEAD_ERR_CUDA;                                                      \
+        }                                                                                  \
+    } while (0)
+
+#define B200_LAUNCH_OK(what)                                                               \
+    do {                                                                                   \
+        cudaError_t _e = cudaGetLastError();                                               \
+        if (_e != cudaSuccess) {                                                           \
+            b200::set_error("launch of %s failed: %s", what, cudaGetErrorString(_e));      \
+            return B200HEAD_ERR_CUDA;                                                      \
+        }                                                                                  \
+    } while (0)
+
+}  // namespace b200

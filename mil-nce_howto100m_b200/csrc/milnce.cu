@@ -1,0 +1,460 @@
+// MIL-NCE loss head for sm_100a: host orchestration + the small SIMT kernels
+// around the tcgen05 GEMM core (tc_gemm.cuh).
+//
+// Replaces reference loss.py:10-18 (MILNCELoss.forward) and its autograd.
+//
+// Forward, for the samples [i0, i0+n) this call owns (n == B on one GPU):
+//   stage   video/text -> fp16 operands (power-of-two scaled; fp32 inputs are
+//           split into hi+lo fp16 planes concatenated along K so that three
+//           tensor-core products reproduce the fp32 dot product to ~2^-22)
+//   pass R  S[range, :]   = V[range] . T^T   -> per-tile row log-sum-exp
+//   pass C  S^T[range*K,:] = T[range*K] . V^T -> per-tile row log-sum-exp
+//           (the column statistic of loss.py:16 as a row statistic of S^T)
+//   final   row_i, col_i, nom_i (exact fp32 dots), den_i = logaddexp(row_i, col_i),
+//           loss = sum(den - nom) / B
+// Backward (closed form):
+//   pass R  recompute S tile -> G  (n, B*K)  fp16 (x 2^13)     [never fp32, never S]
+//   pass C  recompute S^T tile -> G^T (n*K, B)
+//   dvideo = G . T, dtext = G^T . V  (two more tcgen05 GEMMs, fp32 out)
+#include <algorithm>
+
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "tc_gemm.cuh"
+
+namespace {
+
+using b200::align_up;
+
+constexpr int BLOCK_N = 128;
+
+// Device-side scalars shared between kernels of one call.
+struct Scalars {
+    unsigned int absmax_bits[2];  // |video|max, |text|max as float bits
+    float s_video, s_text;        // power-of-two staging scales
+    float inv_ss;                 // 1 / (s_video * s_text): un-scales S
+    float alpha_dvideo;           // grad_loss / (B * 2^13 * s_text)
+    float alpha_dtext;            // grad_loss / (B * 2^13 * s_video)
+    float pad;
+};
+
+struct Plan {
+    int B, K, D, dtype, i0, n;
+    int P;               // K-planes: 1 (bf16 inputs) or 3 (fp32 inputs: hi|lo|hi x hi|hi|lo)
+    long long BK;
+    long long ld_vk, ld_tk;  // leading dims of the K-major staged operands (cols = P*D)
+    long long ld_vt, ld_tt;  // transposed operands: Vt (D, P*B), Tt (D, P*BK)
+    long long ld_g, ld_gt;   // G (n, P*BK), Gt (n*K, P*B)
+    int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
+    size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_g, off_gt, total;
+};
+
+bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
+    if (B <= 0 || K <= 0 || D <= 0 || n <= 0 || i0 < 0 || i0 + n > B) return false;
+    if (dtype != B200HEAD_F32 && dtype != B200HEAD_BF16) return false;
+    p.B = B; p.K = K; p.D = D; p.dtype = dtype; p.i0 = i0; p.n = n;
+    p.P = (dtype == B200HEAD_F32) ? 3 : 1;
+    p.BK = (long long)B * K;
+    p.ld_vk = p.ld_tk = (long long)align_up((size_t)p.P * D, 8);
+    p.ld_vt = (long long)align_up((size_t)p.P * B, 8);
+    p.ld_tt = (long long)align_up((size_t)p.P * p.BK, 8);
+    p.ld_g = p.ld_tt;
+    p.ld_gt = p.ld_vt;
+    p.nb_r = (int)((p.BK + BLOCK_N - 1) / BLOCK_N);
+    p.nb_c = (B + BLOCK_N - 1) / BLOCK_N;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 1024); return r; };
+    p.off_scal = take(sizeof(Scalars));
+    p.off_vk = take((size_t)B * p.ld_vk * 2);
+    p.off_tk = take((size_t)p.BK * p.ld_tk * 2);
+    p.off_vt = take((size_t)D * p.ld_vt * 2);
+    p.off_tt = take((size_t)D * p.ld_tt * 2);
+    p.off_pr = take((size_t)p.nb_r * n * 4);
+    p.off_pc = take((size_t)p.nb_c * n * K * 4);
+    p.off_diff = take((size_t)n * 4);
+    p.off_g = take((size_t)n * p.ld_g * 2);
+    p.off_gt = take((size_t)n * K * p.ld_gt * 2);
+    p.total = o;
+    return true;
+}
+
+// ----------------------------------------------------------------------------
+// staging kernels
+// ----------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f32(T x);
+template <> __device__ __forceinline__ float to_f32<float>(float x) { return x; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 x) {
+    return __bfloat162float(x);
+}
+
+template <typename T>
+__global__ void absmax_kernel(const T *__restrict__ x, size_t count, unsigned int *out_bits) {
+    float m = 0.f;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count;
+         i += (size_t)gridDim.x * blockDim.x) {
+        float v = fabsf(to_f32(x[i]));
+        if (v == v && v <= 3.0e38f) m = fmaxf(m, v);  // ignore NaN/inf for the scale choice
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out_bits, __float_as_uint(m));
+}
+
+// scale = 2^(13 - floor(log2(absmax))): staged magnitudes land in [2^13, 2^14) < fp16 max
+__device__ __forceinline__ float pow2_scale(unsigned int absmax_bits) {
+    if (absmax_bits == 0) return 1.f;
+    int e = (int)((absmax_bits >> 23) & 0xff) - 127;  // floor(log2) for normal floats
+    if (((absmax_bits >> 23) & 0xff) == 0) e = -126;
+    int k = 13 - e;
+    k = max(-100, min(100, k));
+    return exp2f((float)k);
+}
+
+__global__ void scalars_forward_kernel(Scalars *s) {
+    float sv = pow2_scale(s->absmax_bits[0]);
+    float st = pow2_scale(s->absmax_bits[1]);
+    s->s_video = sv;
+    s->s_text = st;
+    s->inv_ss = (1.f / sv) * (1.f / st);
+}
+
+__global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, int B) {
+    const float g = grad_loss[0] / ((float)B * tc::G_SCALE);
+    s->alpha_dvideo = g / s->s_text;
+    s->alpha_dtext = g / s->s_video;
+}
+
+// Plane order along K.  A-side [hi | lo | hi], B-side [hi | hi | lo]:
+// sum_k A'[k] B'[k] = hi.hi + lo.hi + hi.lo  (the lo.lo term, ~2^-22, is dropped).
+__device__ __forceinline__ void split_store(float xs, int planes, bool a_side, __half *dst,
+                                            long long plane_stride) {
+    const __half h = __float2half_rn(xs);
+    dst[0] = h;
+    if (planes == 3) {
+        const __half l = __float2half_rn(xs - __half2float(h));
+        dst[plane_stride] = a_side ? l : h;
+        dst[2 * plane_stride] = a_side ? h : l;
+    }
+}
+
+// in (rows, D) -> outk (rows, planes*D) K-major [a_side order]
+//              -> outt (D, planes*rows) transposed [B-side order] (optional)
+template <typename T>
+__global__ void stage_operand_kernel(const T *__restrict__ in, int rows, int D,
+                                     const float *__restrict__ scale_ptr, int planes, bool a_side,
+                                     __half *__restrict__ outk, long long ldk,
+                                     __half *__restrict__ outt, long long ldt) {
+    __shared__ float tile[32][33];
+    const float sc = *scale_ptr;
+    const int r0 = blockIdx.y * 32, d0 = blockIdx.x * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int r = r0 + j, d = d0 + threadIdx.x;
+        float v = 0.f;
+        if (r < rows && d < D) {
+            v = to_f32(in[(size_t)r * D + d]) * sc;
+            split_store(v, planes, a_side, outk + (size_t)r * ldk + d, D);
+        }
+        tile[j][threadIdx.x] = v;
+    }
+    if (outt == nullptr) return;
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int d = d0 + j, r = r0 + threadIdx.x;
+        if (r < rows && d < D)
+            split_store(tile[threadIdx.x][j], planes, false, outt + (size_t)d * ldt + r, rows);
+    }
+}
+
+// ----------------------------------------------------------------------------
+// finalize: one warp per owned sample
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ float warp_max(float v) {
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <typename T>
+__global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict__ text,
+                                const float *__restrict__ part_r, const float *__restrict__ part_c,
+                                int B, int K, int D, int i0, int n, int nb_r, int nb_c,
+                                float *__restrict__ den, float *__restrict__ nom,
+                                float *__restrict__ diff) {
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= n) return;
+    const int i = i0 + w;
+    // row statistic: lse over the n-blocks of pass R
+    float m = -INFINITY;
+    for (int t = lane; t < nb_r; t += 32) m = fmaxf(m, part_r[(size_t)t * n + w]);
+    m = warp_max(m);
+    float s = 0.f;
+    for (int t = lane; t < nb_r; t += 32) s += expf(part_r[(size_t)t * n + w] - m);
+    const float row = m + logf(warp_sum(s));
+    // column statistic: lse over the n-blocks of pass C and the K candidates of sample i
+    const int nk = n * K;
+    m = -INFINITY;
+    for (int t = lane; t < nb_c * K; t += 32)
+        m = fmaxf(m, part_c[(size_t)(t / K) * nk + (size_t)w * K + (t % K)]);
+    m = warp_max(m);
+    s = 0.f;
+    for (int t = lane; t < nb_c * K; t += 32)
+        s += expf(part_c[(size_t)(t / K) * nk + (size_t)w * K + (t % K)] - m);
+    const float col = m + logf(warp_sum(s));
+    // positives: exact fp32 dot products <v_i, t_{iK+k}>  (loss.py:13-15)
+    float pm = -INFINITY, ps = 0.f;
+    const T *v = video + (size_t)i * D;
+    for (int k = 0; k < K; ++k) {
+        const T *t = text + ((size_t)i * K + k) * D;
+        float acc = 0.f;
+        for (int d = lane; d < D; d += 32) acc = fmaf(to_f32(v[d]), to_f32(t[d]), acc);
+        acc = warp_sum(acc);
+        if (acc > pm) {
+            ps = ps * expf(pm - acc) + 1.f;
+            pm = acc;
+        } else {
+            ps += expf(acc - pm);
+        }
+    }
+    const float nm = pm + logf(ps);
+    const float hi = fmaxf(row, col), lo = fminf(row, col);
+    const float dn = hi + log1pf(expf(lo - hi));
+    if (lane == 0) {
+        den[i] = dn;
+        nom[i] = nm;
+        diff[w] = dn - nm;
+    }
+}
+
+// deterministic single-block reduction: loss = sum(diff) / B, accumulated in double
+__global__ void loss_reduce_kernel(const float *__restrict__ diff, int n, int B, float *loss) {
+    __shared__ double sh[32];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += (double)diff[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        acc = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (threadIdx.x == 0) loss[0] = (float)(acc / (double)B);
+    }
+}
+
+// ----------------------------------------------------------------------------
+// host helpers
+// ----------------------------------------------------------------------------
+int num_sms() {
+    static thread_local int dev_cached = -1, sms = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev != dev_cached) {
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        dev_cached = dev;
+    }
+    return sms > 0 ? sms : 148;
+}
+
+template <class Epi>
+int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
+                const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
+    using L = tc::SmemLayout<BLOCK_N>;
+    CUtensorMap ma, mb;
+    int rc = b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda, tc::BLOCK_M);
+    if (rc) return rc;
+    rc = b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, BLOCK_N);
+    if (rc) return rc;
+    auto kern = tc::gemm_tn_kernel<BLOCK_N, Epi>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    const int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
+    const int grid = tiles < num_sms() ? tiles : num_sms();
+    tc::GemmShape shape{M, N, Kd};
+    kern<<<grid, tc::NUM_THREADS, L::TOTAL, stream>>>(ma, mb, shape, ep);
+    B200_LAUNCH_OK(what);
+    return 0;
+}
+
+template <typename T>
+int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cudaStream_t st) {
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    B200_CUDA_OK(cudaMemsetAsync(sc, 0, sizeof(Scalars), st));
+    const size_t cv = (size_t)p.B * p.D, ct = (size_t)p.BK * p.D;
+    absmax_kernel<T><<<(unsigned)std::min<size_t>((cv + 1023) / 1024, 1184), 256, 0, st>>>(
+        video, cv, &sc->absmax_bits[0]);
+    absmax_kernel<T><<<(unsigned)std::min<size_t>((ct + 1023) / 1024, 1184), 256, 0, st>>>(
+        text, ct, &sc->absmax_bits[1]);
+    scalars_forward_kernel<<<1, 1, 0, st>>>(sc);
+    dim3 blk(32, 8);
+    dim3 gv((p.D + 31) / 32, (p.B + 31) / 32), gt((p.D + 31) / 32, (unsigned)((p.BK + 31) / 32));
+    stage_operand_kernel<T><<<gv, blk, 0, st>>>(video, p.B, p.D, &sc->s_video, p.P, true,
+                                                reinterpret_cast<__half *>(ws + p.off_vk), p.ld_vk,
+                                                reinterpret_cast<__half *>(ws + p.off_vt), p.ld_vt);
+    stage_operand_kernel<T><<<gt, blk, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, p.P, false,
+                                                reinterpret_cast<__half *>(ws + p.off_tk), p.ld_tk,
+                                                reinterpret_cast<__half *>(ws + p.off_tt), p.ld_tt);
+    B200_LAUNCH_OK("staging kernels");
+    return 0;
+}
+
+int check_common(const Plan &p, const void *ws, size_t ws_bytes) {
+    if (ws == nullptr || ((uintptr_t)ws & 255)) {
+        b200::set_error("workspace must be non-null and 256-byte aligned");
+        return B200HEAD_ERR_WS;
+    }
+    if (ws_bytes < p.total) {
+        b200::set_error("workspace too small: need %zu bytes, got %zu", p.total, ws_bytes);
+        return B200HEAD_ERR_WS;
+    }
+    if ((long long)p.B * p.K > 2000000000ll || (long long)p.P * p.BK > 2000000000ll) {
+        b200::set_error("B*K too large for 32-bit tile indexing");
+        return B200HEAD_ERR_ARG;
+    }
+    return 0;
+}
+
+template <typename T>
+int forward_impl(const Plan &p, const T *video, const T *text, float *den, float *nom, float *loss,
+                 uint8_t *ws, cudaStream_t st) {
+    int rc = stage_inputs<T>(p, video, text, ws, st);
+    if (rc) return rc;
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
+    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    float *pr = reinterpret_cast<float *>(ws + p.off_pr);
+    float *pc = reinterpret_cast<float *>(ws + p.off_pc);
+    float *diff = reinterpret_cast<float *>(ws + p.off_diff);
+    const int Kd = p.P * p.D;
+    // pass R: rows = owned video rows, columns = all text rows
+    tc::EpiRowLse::Params er{pr, (long long)p.n, &sc->inv_ss};
+    rc = launch_gemm<tc::EpiRowLse>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n,
+                                    (int)p.BK, Kd, er, st, "milnce forward pass R");
+    if (rc) return rc;
+    // pass C: rows = owned text rows, columns = all video rows
+    tc::EpiRowLse::Params ec{pc, (long long)p.n * p.K, &sc->inv_ss};
+    rc = launch_gemm<tc::EpiRowLse>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk,
+                                    p.n * p.K, p.B, Kd, ec, st, "milnce forward pass C");
+    if (rc) return rc;
+    const int warps_per_block = 8;
+    finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
+        video, text, pr, pc, p.B, p.K, p.D, p.i0, p.n, p.nb_r, p.nb_c, den, nom, diff);
+    loss_reduce_kernel<<<1, 1024, 0, st>>>(diff, p.n, p.B, loss);
+    B200_LAUNCH_OK("milnce finalize");
+    return 0;
+}
+
+template <typename T>
+int backward_impl(const Plan &p, const T *video, const T *text, const float *den, const float *nom,
+                  const float *grad_loss, float *dvideo, float *dtext, int reuse, uint8_t *ws,
+                  cudaStream_t st) {
+    int rc;
+    if (!reuse) {
+        rc = stage_inputs<T>(p, video, text, ws, st);
+        if (rc) return rc;
+    }
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    scalars_backward_kernel<<<1, 1, 0, st>>>(sc, grad_loss, p.B);
+    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
+    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
+    const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
+    __half *g = reinterpret_cast<__half *>(ws + p.off_g);
+    __half *gt = reinterpret_cast<__half *>(ws + p.off_gt);
+    const int Kd = p.P * p.D;
+    // pass R: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, p.K, &sc->inv_ss};
+    rc = launch_gemm<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
+                               gr, st, "milnce backward pass R");
+    if (rc) return rc;
+    // pass C: G^T (n*K, B): row r <-> sample (i0*K + r) / K, column <-> sample index itself
+    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, p.K, 1, &sc->inv_ss};
+    rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
+                               p.B, Kd, gc, st, "milnce backward pass C");
+    if (rc) return rc;
+    // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
+    rc = launch_gemm<tc::EpiStore>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)(p.P * p.BK), sv, st,
+                                   "milnce dvideo GEMM");
+    if (rc) return rc;
+    // dtext (n*K, D) = G^T . V   : A = Gt (n*K, P*B), Bm = Vt (D, P*B)
+    tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext};
+    rc = launch_gemm<tc::EpiStore>(gt, p.ld_gt, vt, p.ld_vt, p.n * p.K, p.D, p.P * p.B, sd, st,
+                                   "milnce dtext GEMM");
+    return rc;
+}
+
+}  // namespace
+
+extern "C" size_t milnce_workspace_bytes(int B, int K, int D, int dtype, int n) {
+    Plan p;
+    if (!make_plan(p, B, K, D, dtype, 0, n)) return 0;
+    return p.total;
+}
+
+extern "C" int milnce_forward(const void *video, const void *text, int B, int K, int D, int dtype,
+                              int i0, int n, float *den, float *nom, float *loss, void *workspace,
+                              size_t workspace_bytes, void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, dtype, i0, n)) {
+        b200::set_error("milnce_forward: bad shape/range B=%d K=%d D=%d dtype=%d i0=%d n=%d", B, K, D,
+                        dtype, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!video || !text || !den || !nom || !loss) {
+        b200::set_error("milnce_forward: null pointer argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *ws = (uint8_t *)workspace;
+    if (dtype == B200HEAD_F32)
+        return forward_impl<float>(p, (const float *)video, (const float *)text, den, nom, loss, ws, st);
+    return forward_impl<__nv_bfloat16>(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text,
+                                       den, nom, loss, ws, st);
+}
+
+extern "C" int milnce_backward(const void *video, const void *text, const float *den,
+                               const float *nom, const float *grad_loss, float *dvideo,
+                               float *dtext, int B, int K, int D, int dtype, int i0, int n,
+                               int reuse_forward_ws, void *workspace, size_t workspace_bytes,
+                               void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, dtype, i0, n)) {
+        b200::set_error("milnce_backward: bad shape/range B=%d K=%d D=%d dtype=%d i0=%d n=%d", B, K,
+                        D, dtype, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!video || !text || !den || !nom || !grad_loss || !dvideo || !dtext) {
+        b200::set_error("milnce_backward: null pointer argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *ws = (uint8_t *)workspace;
+    if (dtype == B200HEAD_F32)
+        return backward_impl<float>(p, (const float *)video, (const float *)text, den, nom, grad_loss,
+                                    dvideo, dtext, reuse_forward_ws, ws, st);
+    return backward_impl<__nv_bfloat16>(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text,
+                                        den, nom, grad_loss, dvideo, dtext, reuse_forward_ws, ws, st);
+}
+
+extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
+                                    int lda, int ldb, int ldc, float alpha, void *stream) {
+    if (!A || !Bm || !C || M <= 0 || N <= 0 || Kd <= 0) {
+        b200::set_error("b200head_gemm_tn_f16: bad argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, ep, (cudaStream_t)stream,
+                                     "gemm_tn_f16 test hook");
+}

@@ -1,0 +1,126 @@
+"""Drop-in for the reference's ``loss.py::MILNCELoss`` (reference loss.py:6-18).
+
+Same constructor, same ``forward(video_embd, text_embd)`` -> 0-d tensor, same
+gradients; the B x B*K similarity matrix is never materialised in fp32 and the
+host->device copy of ``eye(B)`` the reference does per call (loss.py:13) is gone.
+All arithmetic runs in libb200head.so (hand-written sm_100a kernels); there is no
+PyTorch or CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return _lib.F32
+    if t.dtype == torch.bfloat16:
+        return _lib.BF16
+    raise TypeError(f"MILNCELoss supports float32 and bfloat16 embeddings, got {t.dtype}")
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr())
+
+
+class CudaBackend:
+    """The product backend: calls the C ABI on the tensors' CUDA device."""
+
+    @staticmethod
+    def forward(video, text, i0, n):
+        """Returns (loss_part[1], den[B], nom[B], workspace) for samples [i0, i0+n)."""
+        lib = _lib.load()
+        B, D = video.shape
+        K = text.shape[0] // B
+        code = _dtype_code(video)
+        dev = video.device
+        nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        den = torch.empty(B, dtype=torch.float32, device=dev)
+        nom = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_forward(_ptr(video), _ptr(text), B, K, D, code, i0, n, _ptr(den),
+                                    _ptr(nom), _ptr(loss), _ptr(ws), nbytes, _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_forward")
+        return loss, den, nom, ws
+
+    @staticmethod
+    def backward(video, text, den, nom, grad_loss, i0, n, ws):
+        """Returns float32 (dvideo (n, D), dtext (n*K, D)): the rows this range owns."""
+        lib = _lib.load()
+        B, D = video.shape
+        K = text.shape[0] // B
+        code = _dtype_code(video)
+        dev = video.device
+        reuse = 1
+        if ws is None:
+            nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            reuse = 0
+        dv = torch.empty(n, D, dtype=torch.float32, device=dev)
+        dt = torch.empty(n * K, D, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_backward(_ptr(video), _ptr(text), _ptr(den), _ptr(nom), _ptr(grad_loss),
+                                     _ptr(dv), _ptr(dt), B, K, D, code, i0, n, reuse, _ptr(ws),
+                                     ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_backward")
+        return dv, dt
+
+
+def _validate(video_embd, text_embd):
+    if video_embd.dim() != 2 or text_embd.dim() != 2:
+        raise ValueError("video_embd must be (B, D) and text_embd (B*K, D)")
+    if video_embd.shape[1] != text_embd.shape[1]:
+        raise ValueError("embedding widths differ")
+    b = video_embd.shape[0]
+    if b == 0 or text_embd.shape[0] == 0 or text_embd.shape[0] % b != 0:
+        # the reference's x.view(B, B, -1) (loss.py:12) raises here as well
+        raise ValueError("text_embd rows must be a positive multiple of video_embd rows")
+    if video_embd.dtype != text_embd.dtype:
+        raise TypeError("video_embd and text_embd must share a dtype")
+    if not (video_embd.is_cuda and text_embd.is_cuda):
+        raise RuntimeError("MILNCELoss runs on CUDA tensors only (no CPU path)")
+    if video_embd.device != text_embd.device:
+        raise RuntimeError("video_embd and text_embd live on different devices")
+    _dtype_code(video_embd)
+
+
+class _MILNCEFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, video_embd, text_embd):
+        _validate(video_embd, text_embd)
+        v = video_embd.detach().contiguous()
+        t = text_embd.detach().contiguous()
+        loss, den, nom, ws = CudaBackend.forward(v, t, 0, v.shape[0])
+        ctx.save_for_backward(v, t, den, nom)
+        ctx.ws = ws
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        v, t, den, nom = ctx.saved_tensors
+        g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
+        dv, dt = CudaBackend.backward(v, t, den, nom, g, 0, v.shape[0], ctx.ws)
+        ctx.ws = None
+        return dv.to(v.dtype), dt.to(t.dtype)
+
+
+class MILNCELoss(torch.nn.Module):
+    """``MILNCELoss()(video_embd, text_embd)`` - see reference loss.py:6-18.
+
+    video_embd: (B, D); text_embd: (B*K, D) with the K candidates of a sample
+    contiguous.  Returns ``mean_i(log sum over row i and column-group i of
+    exp(S) - log sum_k exp(S[i, i, k]))`` as a float32 0-d tensor (the reference
+    returns float32 for bf16 inputs too, because its mask is float32).
+    """
+
+    def __init__(self):
+        super().__init__()
+
+    def forward(self, video_embd, text_embd):
+        return _MILNCEFunction.apply(video_embd, text_embd)

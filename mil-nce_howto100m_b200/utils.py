@@ -1,0 +1,115 @@
+"""Drop-in for the reference's ``utils.py::AllGather`` (utils.py:8-24) and the
+fused gather -> loss module for the train-step call site
+(main_distributed.py:233-238, train.py:217-221).
+
+``AllGather.apply(tensor, args)`` keeps the reference's contract - forward
+returns the rank-ordered concatenation, backward returns only the local slice of
+the incoming gradient with NO reduction (utils.py:20-24) - but gathers with one
+``all_gather_into_tensor`` straight into the output buffer (no list of temporaries,
+no ``torch.cat`` copy).
+
+``GatheredMILNCELoss`` goes further: every rank computes only
+the row block and the column block of the similarity matrix that its own samples
+need, so the loss is sharded instead of being recomputed in full on every rank as
+in the reference.  It returns the same global-mean loss on every rank and the same
+local gradients ``AllGather.backward`` would deliver.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def _world(args=None):
+    if args is not None and hasattr(args, "world_size"):
+        return int(args.world_size), int(args.rank)
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(), dist.get_rank()
+    return 1, 0
+
+
+class AllGather(torch.autograd.Function):
+    """An autograd function that performs allgather on a tensor (reference utils.py:8-24)."""
+
+    @staticmethod
+    def forward(ctx, tensor, args):
+        world, rank = _world(args)
+        ctx.rank = rank
+        ctx.batch_size = tensor.shape[0]
+        t = tensor.contiguous()
+        if world == 1:
+            return t.clone()
+        out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        return (
+            grad_output[ctx.batch_size * ctx.rank: ctx.batch_size * (ctx.rank + 1)],
+            None,
+        )
+
+
+class _GatheredMILNCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, video_local, text_local, world, rank, group, backend):
+        b = video_local.shape[0]
+        v = video_local.detach().contiguous()
+        t = text_local.detach().contiguous()
+        if world > 1:
+            V = torch.empty((world * b, v.shape[1]), dtype=v.dtype, device=v.device)
+            T = torch.empty((world * t.shape[0], t.shape[1]), dtype=t.dtype, device=t.device)
+            h1 = dist.all_gather_into_tensor(V, v, group=group, async_op=True)
+            h2 = dist.all_gather_into_tensor(T, t, group=group, async_op=True)
+            h1.wait()
+            h2.wait()
+        else:
+            V, T = v, t
+        i0 = rank * b
+        loss_part, den, nom, ws = backend.forward(V, T, i0, b)
+        if world > 1:
+            # 4*B bytes: every rank needs den of every sample for its column block
+            den_all = torch.empty_like(den)
+            dist.all_gather_into_tensor(den_all, den[i0:i0 + b].contiguous(), group=group)
+            dist.all_reduce(loss_part, op=dist.ReduceOp.SUM, group=group)
+            den = den_all
+        ctx.save_for_backward(V, T, den, nom)
+        ctx.ws = ws
+        ctx.meta = (i0, b, backend, v.dtype, t.dtype)
+        return loss_part[0]
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        V, T, den, nom = ctx.saved_tensors
+        i0, b, backend, vdt, tdt = ctx.meta
+        g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
+        dv, dt = backend.backward(V, T, den, nom, g, i0, b, ctx.ws)
+        ctx.ws = None
+        # exactly the slice AllGather.backward returns: no gradient collective (utils.py:20-24)
+        return dv.to(vdt), dt.to(tdt), None, None, None, None
+
+
+class GatheredMILNCELoss(torch.nn.Module):
+    """allgather(video), allgather(text), MILNCELoss - fused and sharded.
+
+    Replaces the three lines ``video_embd = allgather(video_embd, args); text_embd =
+    allgather(text_embd, args); loss = loss_fun(video_embd, text_embd)``
+    (main_distributed.py:235-237).  Inputs are the LOCAL (b, D) / (b*K, D)
+    embeddings of this rank.
+    """
+
+    def __init__(self, args=None, group=None, backend=None):
+        super().__init__()
+        self.args = args
+        self.group = group
+        self._backend = backend
+
+    def forward(self, video_embd, text_embd):
+        from .loss import CudaBackend, _validate
+        backend = self._backend
+        if backend is None:
+            _validate(video_embd, text_embd)
+            backend = CudaBackend
+        world, rank = _world(self.args)
+        return _GatheredMILNCE.apply(video_embd, text_embd, world, rank, self.group, backend)

@@ -1,0 +1,11 @@
+"""Importable alias for the package directory ``mil-nce_howto100m_b200`` (its name,
+fixed by the project layout, is not a valid Python identifier)."""
+import importlib
+import os
+import sys
+
+_root = os.path.dirname(os.path.abspath(__file__))
+if _root not in sys.path:
+    sys.path.insert(0, _root)
+_pkg = importlib.import_module("mil-nce_howto100m_b200")
+sys.modules[__name__] = _pkg

@@ -1,0 +1,149 @@
+"""MIL-NCE CUDA path against the CPU oracle and the golden fixtures (GPU).
+
+Tolerances are BASELINE.json's: 1e-5 relative for float32 inputs, 1e-3 for
+bfloat16 inputs (oracle evaluated in float64 on the bf16-rounded inputs, gradients
+compared on the kernel's float32 outputs - SURVEY.md F9).  "Relative" is norm-wise
+for gradients, |a-b|/|b| for the scalar loss."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import milnce_b200
+from conftest import GOLDEN, rel_err
+from milnce_b200.loss import CudaBackend
+from oracle import milnce_oracle
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: 1e-5, torch.bfloat16: 1e-3}
+
+
+def _run(v, t, grad=1.0):
+    v = v.clone().requires_grad_(True)
+    t = t.clone().requires_grad_(True)
+    loss = milnce_b200.MILNCELoss()(v, t)
+    (loss * grad).backward()
+    torch.cuda.synchronize()
+    return loss.detach(), v.grad, t.grad
+
+
+def _raw(v, t):
+    """fp32 gradients straight from the C ABI (no cast to the input dtype)."""
+    B = v.shape[0]
+    loss, den, nom, ws = CudaBackend.forward(v, t, 0, B)
+    g = torch.ones(1, device="cuda")
+    dv, dt = CudaBackend.backward(v, t, den, nom, g, 0, B, ws)
+    torch.cuda.synchronize()
+    return loss[0], dv, dt, den, nom
+
+
+def _check(v, t, dtype, name):
+    vd, td = v.cuda().to(dtype), t.cuda().to(dtype)
+    ref_loss, ref_dv, ref_dt, ref_den, ref_nom = milnce_oracle.milnce_closed_form(
+        vd.double().cpu().numpy(), td.double().cpu().numpy())
+    loss, dv, dt, den, nom = _raw(vd, td)
+    e_loss = abs(loss.item() - ref_loss) / abs(ref_loss)
+    e_den = np.max(np.abs(den.cpu().numpy() - ref_den) / np.abs(ref_den))
+    e_dv = rel_err(dv.cpu().numpy(), ref_dv)
+    e_dt = rel_err(dt.cpu().numpy(), ref_dt)
+    print(f"{name} {dtype}: loss {e_loss:.2e} den {e_den:.2e} dV {e_dv:.2e} dT {e_dt:.2e}")
+    tol = TOL[dtype]
+    assert e_loss < tol and e_den < tol and e_dv < tol and e_dt < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "milnce_*.npz"))),
+                         ids=os.path.basename)
+def test_golden_fixture(path, dtype):
+    g = np.load(path)
+    v, t = torch.from_numpy(g["video"]), torch.from_numpy(g["text"])
+    _check(v, t, dtype, os.path.basename(path))
+    if dtype == torch.float32:
+        # and directly against the numbers the executed reference produced
+        loss, dv, dt = _run(v.cuda(), t.cuda())
+        assert abs(loss.item() - float(g["loss"])) / abs(float(g["loss"])) < 1e-5
+        assert rel_err(dv.cpu().numpy(), g["dvideo"]) < 1e-5
+        assert rel_err(dt.cpu().numpy(), g["dtext"]) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,K,D,scale", [
+    (256, 4, 512, 0.05),
+    (256, 4, 512, 0.5),     # logits reach +-30: exercises the online max
+    (1000, 3, 264, 0.2),    # ragged tiles, odd K
+    (129, 1, 8, 1.0),       # K = 1, tiny D
+    (5, 7, 24, 0.4),        # fewer rows than a tile
+])
+def test_random_shapes(B, K, D, scale, dtype):
+    g = torch.Generator().manual_seed(B + K + D)
+    v = torch.randn(B, D, generator=g) * scale
+    t = torch.randn(B * K, D, generator=g) * scale
+    _check(v, t, dtype, f"B{B}K{K}D{D}s{scale}")
+
+
+def test_module_api_dtypes_and_grad_scale():
+    g = torch.Generator().manual_seed(3)
+    v = (torch.randn(64, 128, generator=g) * 0.2).cuda()
+    t = (torch.randn(256, 128, generator=g) * 0.2).cuda()
+    loss1, dv1, dt1 = _run(v, t, 1.0)
+    loss2, dv2, dt2 = _run(v, t, 2.5)
+    assert loss1.dim() == 0 and loss1.dtype == torch.float32
+    assert torch.allclose(dv2, 2.5 * dv1, rtol=1e-6, atol=0) and torch.allclose(dt2, 2.5 * dt1, rtol=1e-6, atol=0)
+    lb, dvb, dtb = _run(v.bfloat16(), t.bfloat16())
+    assert lb.dtype == torch.float32 and dvb.dtype == torch.bfloat16 and dtb.dtype == torch.bfloat16
+    # non-contiguous inputs are accepted like any torch module
+    vt = v.t().contiguous().t()
+    l3, _, _ = _run(vt, t)
+    assert abs(l3.item() - loss1.item()) < 1e-6
+
+
+def test_sharded_ranges_tile_the_full_problem():
+    """Four 'ranks' emulated on one GPU: the union of their range calls equals the
+    single-GPU result (what AllGather.backward slices would deliver)."""
+    B, K, D, W = 512, 4, 256, 4
+    g = torch.Generator().manual_seed(9)
+    v = (torch.randn(B, D, generator=g) * 0.3).cuda()
+    t = (torch.randn(B * K, D, generator=g) * 0.3).cuda()
+    loss, dv, dt, den, nom = _raw(v, t)
+    b = B // W
+    parts = [CudaBackend.forward(v, t, r * b, b) for r in range(W)]
+    den_all = torch.cat([p[1][r * b:(r + 1) * b] for r, p in enumerate(parts)])
+    nom_all = torch.cat([p[2][r * b:(r + 1) * b] for r, p in enumerate(parts)])
+    loss_sum = sum(p[0] for p in parts)
+    assert torch.allclose(den_all, den, rtol=1e-6, atol=0) and torch.allclose(nom_all, nom, rtol=1e-6)
+    assert abs(loss_sum.item() - loss.item()) < 1e-5 * abs(loss.item())
+    one = torch.ones(1, device="cuda")
+    for r, p in enumerate(parts):
+        dvr, dtr = CudaBackend.backward(v, t, den_all, nom_all, one, r * b, b, p[3])
+        assert rel_err(dvr.cpu().numpy(), dv[r * b:(r + 1) * b].cpu().numpy()) < 2e-6
+        assert rel_err(dtr.cpu().numpy(), dt[r * b * K:(r + 1) * b * K].cpu().numpy()) < 2e-6
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_full_size_config(dtype):
+    """BASELINE.json configs[1]: B=8192, K=4, D=512.  Checked against the float64
+    torch port run on the same GPU (the numpy oracle would take minutes), plus two
+    size-independent properties: den >= nom, and sum_i dV_i . v_i == sum_c dT_c . t_c
+    (both equal sum_ic G_ic S_ic)."""
+    B, K, D = 8192, 4, 512
+    g = torch.Generator().manual_seed(0)
+    v = (torch.randn(B, D, generator=g) * 0.05).cuda().to(dtype)
+    t = (torch.randn(B * K, D, generator=g) * 0.05).cuda().to(dtype)
+    loss, dv, dt, den, nom = _raw(v, t)
+    assert bool((den >= nom).all())
+    lhs = (dv.double() * v.double()).sum().item()
+    rhs = (dt.double() * t.double()).sum().item()
+    assert abs(lhs - rhs) < 1e-4 * max(abs(lhs), 1e-12)
+    vd = v.double().requires_grad_(True)
+    td = t.double().requires_grad_(True)
+    ref = milnce_oracle.milnce_torch_lean(vd, td)
+    ref.backward()
+    tol = TOL[dtype]
+    e_loss = abs(loss.item() - ref.item()) / abs(ref.item())
+    e_dv = ((dv.double() - vd.grad).norm() / vd.grad.norm()).item()
+    e_dt = ((dt.double() - td.grad).norm() / td.grad.norm()).item()
+    print(f"full size {dtype}: loss {e_loss:.2e} dV {e_dv:.2e} dT {e_dt:.2e}")
+    assert e_loss < tol and e_dv < tol and e_dt < tol
