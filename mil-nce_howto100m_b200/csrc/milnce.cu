@@ -47,6 +47,7 @@ struct Plan {
     long long ld_vt, ld_tt;  // transposed operands: Vt (D, P*B), Tt (D, P*BK)
     long long ld_g, ld_gt;   // G (n, P*BK), Gt (n*K, P*B)
     int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
+    int chunk_s, chunk_g;    // k-blocks per tensor-core accumulation chunk (S passes / grad GEMMs)
     size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_g, off_gt, total;
 };
 
@@ -55,6 +56,10 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     if (dtype != B200HEAD_F32 && dtype != B200HEAD_BF16) return false;
     p.B = B; p.K = K; p.D = D; p.dtype = dtype; p.i0 = i0; p.n = n;
     p.P = (dtype == B200HEAD_F32) ? 3 : 1;
+    // fp32 inputs: 8 MMA steps per chunk (truncation bias ~5e-7); bf16 inputs: the
+    // similarity in one chunk (<= 32 steps at D=512), gradient GEMMs in 64-step chunks.
+    p.chunk_s = (dtype == B200HEAD_F32) ? 2 : 16;
+    p.chunk_g = (dtype == B200HEAD_F32) ? 2 : 16;
     p.BK = (long long)B * K;
     p.ld_vk = p.ld_tk = (long long)align_up((size_t)p.P * D, 8);
     p.ld_vt = (long long)align_up((size_t)p.P * B, 8);
@@ -260,7 +265,8 @@ int num_sms() {
 
 template <class Epi>
 int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
-                const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
+                int chunk_iters, const typename Epi::Params &ep, cudaStream_t stream,
+                const char *what) {
     using L = tc::SmemLayout<BLOCK_N>;
     CUtensorMap ma, mb;
     int rc = b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda, tc::BLOCK_M);
@@ -271,7 +277,7 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    tc::GemmShape shape{M, N, Kd};
+    tc::GemmShape shape{M, N, Kd, chunk_iters};
     kern<<<grid, tc::NUM_THREADS, L::TOTAL, stream>>>(ma, mb, shape, ep);
     B200_LAUNCH_OK(what);
     return 0;
@@ -330,12 +336,12 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
     // pass R: rows = owned video rows, columns = all text rows
     tc::EpiRowLse::Params er{pr, (long long)p.n, &sc->inv_ss};
     rc = launch_gemm<tc::EpiRowLse>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n,
-                                    (int)p.BK, Kd, er, st, "milnce forward pass R");
+                                    (int)p.BK, Kd, p.chunk_s, er, st, "milnce forward pass R");
     if (rc) return rc;
     // pass C: rows = owned text rows, columns = all video rows
     tc::EpiRowLse::Params ec{pc, (long long)p.n * p.K, &sc->inv_ss};
     rc = launch_gemm<tc::EpiRowLse>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk,
-                                    p.n * p.K, p.B, Kd, ec, st, "milnce forward pass C");
+                                    p.n * p.K, p.B, Kd, p.chunk_s, ec, st, "milnce forward pass C");
     if (rc) return rc;
     const int warps_per_block = 8;
     finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
@@ -366,21 +372,21 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     // pass R: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, p.K, &sc->inv_ss};
     rc = launch_gemm<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
-                               gr, st, "milnce backward pass R");
+                               p.chunk_s, gr, st, "milnce backward pass R");
     if (rc) return rc;
     // pass C: G^T (n*K, B): row r <-> sample (i0*K + r) / K, column <-> sample index itself
     tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, p.K, 1, &sc->inv_ss};
     rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
-                               p.B, Kd, gc, st, "milnce backward pass C");
+                               p.B, Kd, p.chunk_s, gc, st, "milnce backward pass C");
     if (rc) return rc;
     // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
-    rc = launch_gemm<tc::EpiStore>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)(p.P * p.BK), sv, st,
-                                   "milnce dvideo GEMM");
+    rc = launch_gemm<tc::EpiStore>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)(p.P * p.BK), p.chunk_g,
+                                   sv, st, "milnce dvideo GEMM");
     if (rc) return rc;
     // dtext (n*K, D) = G^T . V   : A = Gt (n*K, P*B), Bm = Vt (D, P*B)
     tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext};
-    rc = launch_gemm<tc::EpiStore>(gt, p.ld_gt, vt, p.ld_vt, p.n * p.K, p.D, p.P * p.B, sd, st,
+    rc = launch_gemm<tc::EpiStore>(gt, p.ld_gt, vt, p.ld_vt, p.n * p.K, p.D, p.P * p.B, p.chunk_g, sd, st,
                                    "milnce dtext GEMM");
     return rc;
 }
@@ -455,6 +461,6 @@ extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int
     int rc = b200::check_device();
     if (rc) return rc;
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
-    return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, ep, (cudaStream_t)stream,
+    return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                      "gemm_tn_f16 test hook");
 }

@@ -6,9 +6,11 @@
 //   warp 0      TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring)
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
 //   warps 2..5  epilogue: tcgen05.ld the fp32 accumulator (one TMEM lane = one
-//               output row per thread) and apply the epilogue functor
-// Accumulators are double-buffered in TMEM (2 x BLOCK_N columns) so the epilogue
-// of tile t overlaps the MMAs of tile t+1.
+//               output row per thread) into registers, then run the epilogue functor
+// Accumulators are double-buffered in TMEM (2 x BLOCK_N columns) and drained to
+// registers per K-chunk, so the epilogue of tile t overlaps the MMAs of tile t+1
+// and long K loops are summed in fp32 registers (round-to-nearest) rather than
+// inside the tensor core (which truncates).
 //
 // The loss kernels never write C: their epilogues reduce the tile on the fly
 // (row log-sum-exp for the MIL-NCE forward, the softmax-gradient tile G for the
@@ -182,10 +184,12 @@ struct EpiCtx {
     int m_blk, n_blk;  // tile coordinates
     int M, N;          // problem extent
     int tid;           // 0..127 within the epilogue warps; row in tile = tid
-    int buf;           // accumulator buffer (0/1), for double-buffered smem scratch
-    uint32_t taddr;    // TMEM address of this thread's lane, column 0 of the accumulator
+    int par;           // tile parity, for double-buffered smem scratch
     float *scratch;    // 2 * BLOCK_N floats of smem private to the epilogue warps
 };
+// Every functor receives the finished fp32 accumulator row of its thread in
+// registers (acc[BLOCK_N], compile-time indexed): the kernel has already drained
+// TMEM, so the tensor core is working on the next tile while the functor runs.
 
 // ---- plain store: C = alpha * acc (dvideo / dtext GEMMs, and the test hook) ----
 struct EpiStore {
@@ -196,28 +200,28 @@ struct EpiStore {
         const float *alpha_dev;  // optional device scalar multiplied into alpha
     };
     template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c) {
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
         float alpha = p.alpha;
         if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
         const int row = c.m0 + c.tid;
-#pragma unroll 1
+        if (row >= c.M) return;
+#pragma unroll
         for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-            float v[32];
-            tmem_ld32(c.taddr + ch * 32, v);
-            if (row >= c.M) continue;
             const int col0 = c.n0 + ch * 32;
+            if (col0 >= c.N) break;
             float *dst = p.C + (long long)row * p.ldc + col0;
             if (col0 + 32 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
-                    float4 o = make_float4(v[i] * alpha, v[i + 1] * alpha, v[i + 2] * alpha,
-                                           v[i + 3] * alpha);
+                    const int e = ch * 32 + i;
+                    float4 o = make_float4(acc[e] * alpha, acc[e + 1] * alpha, acc[e + 2] * alpha,
+                                           acc[e + 3] * alpha);
                     *reinterpret_cast<float4 *>(dst + i) = o;
                 }
             } else {
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
-                    if (col0 + i < c.N) dst[i] = v[i] * alpha;
+                    if (col0 + i < c.N) dst[i] = acc[ch * 32 + i] * alpha;
             }
         }
     }
@@ -232,30 +236,25 @@ struct EpiRowLse {
         const float *scale_dev;  // device scalar: un-does the fp16 staging scale
     };
     template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c) {
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
         const float sc = __ldg(p.scale_dev) * LOG2E;  // work in the log2 domain
-        float mx = -INFINITY, sum = 0.f;
-#pragma unroll 1
-        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-            float v[32];
-            tmem_ld32(c.taddr + ch * 32, v);
-            const int col0 = c.n0 + ch * 32;
-            if (col0 >= c.N) continue;
-            float cm = -INFINITY;
+        float mx = -INFINITY;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                v[i] = (col0 + i < c.N) ? v[i] * sc : -INFINITY;
-                cm = fmaxf(cm, v[i]);
-            }
-            if (cm > mx) {
-                sum *= fast_exp2(mx - cm);  // mx = -inf on the first chunk: exp2(-inf) = 0
-                mx = cm;
-            }
+        for (int i = 0; i < BLOCK_N; ++i) {
+            acc[i] = (c.n0 + i < c.N) ? acc[i] * sc : -INFINITY;
+            mx = fmaxf(mx, acc[i]);
+        }
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) sum += fast_exp2(v[i] - mx);
+        for (int i = 0; i < BLOCK_N; i += 4) {
+            s0 += fast_exp2(acc[i] - mx);
+            s1 += fast_exp2(acc[i + 1] - mx);
+            s2 += fast_exp2(acc[i + 2] - mx);
+            s3 += fast_exp2(acc[i + 3] - mx);
         }
         const int row = c.m0 + c.tid;
-        if (row < c.M) p.part[(long long)c.n_blk * p.ldp + row] = (mx + log2f(sum)) * LN2;
+        if (row < c.M)
+            p.part[(long long)c.n_blk * p.ldp + row] = (mx + log2f((s0 + s1) + (s2 + s3))) * LN2;
     }
 };
 
@@ -277,9 +276,9 @@ struct EpiG {
         const float *scale_dev;
     };
     template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c) {
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
         static_assert(BLOCK_N <= NUM_EPI_THREADS, "one table entry per epilogue thread");
-        float *tab = c.scratch + c.buf * BLOCK_N;  // den of the column's sample, log2 domain
+        float *tab = c.scratch + c.par * BLOCK_N;  // den of the column's sample, log2 domain
         if (c.tid < BLOCK_N) {
             const int n = c.n0 + c.tid;
             tab[c.tid] = (n < c.N) ? __ldg(p.den + n / p.cdiv) * LOG2E : INFINITY;
@@ -296,39 +295,38 @@ struct EpiG {
         const int cs_lo = c.n0 / p.cdiv;
         const int cs_hi = (min(c.n0 + BLOCK_N, c.N) - 1) / p.cdiv;
         const bool diag_tile = !(rs_hi < cs_lo || cs_hi < rs_lo);
-#pragma unroll 1
-        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-            float v[32];
-            tmem_ld32(c.taddr + ch * 32, v);
-            const int col0 = c.n0 + ch * 32;
-            if (col0 >= c.N) continue;  // warp-uniform
-            if (!diag_tile) {
+        if (!diag_tile) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float y = v[i] * sc;
-                    v[i] = fast_exp2(y - dr) + fast_exp2(y - tab[ch * 32 + i]);
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float y = v[i] * sc;
-                    float g = fast_exp2(y - dr) + fast_exp2(y - tab[ch * 32 + i]);
-                    if ((col0 + i) / p.cdiv == rs) g -= fast_exp2(y - nr);  // the positives
-                    v[i] = g;
-                }
+            for (int i = 0; i < BLOCK_N; ++i) {
+                const float y = acc[i] * sc;
+                acc[i] = (fast_exp2(y - dr) + fast_exp2(y - tab[i])) * G_SCALE;
             }
-            if (row >= c.M) continue;  // no warp-collective op below this point
+        } else {
+#pragma unroll
+            for (int i = 0; i < BLOCK_N; ++i) {
+                const float y = acc[i] * sc;
+                float g = fast_exp2(y - dr) + fast_exp2(y - tab[i]);
+                if ((c.n0 + i) / p.cdiv == rs) g -= fast_exp2(y - nr);  // the positives
+                acc[i] = g * G_SCALE;
+            }
+        }
+        if (row >= c.M) return;
+#pragma unroll
+        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+            const int col0 = c.n0 + ch * 32;
+            if (col0 >= c.N) break;
             __half *dst = p.out + (long long)row * p.ldo + col0;
             const bool full = (col0 + 32 <= c.N);
             if (p.planes == 1) {
                 if (full && ((((uintptr_t)dst) & 15) == 0)) {
 #pragma unroll
                     for (int i = 0; i < 32; i += 8) {
+                        const int e = ch * 32 + i;
+                        __half2 h0 = __floats2half2_rn(acc[e], acc[e + 1]);
+                        __half2 h1 = __floats2half2_rn(acc[e + 2], acc[e + 3]);
+                        __half2 h2 = __floats2half2_rn(acc[e + 4], acc[e + 5]);
+                        __half2 h3 = __floats2half2_rn(acc[e + 6], acc[e + 7]);
                         uint4 o;
-                        __half2 h0 = __floats2half2_rn(v[i] * G_SCALE, v[i + 1] * G_SCALE);
-                        __half2 h1 = __floats2half2_rn(v[i + 2] * G_SCALE, v[i + 3] * G_SCALE);
-                        __half2 h2 = __floats2half2_rn(v[i + 4] * G_SCALE, v[i + 5] * G_SCALE);
-                        __half2 h3 = __floats2half2_rn(v[i + 6] * G_SCALE, v[i + 7] * G_SCALE);
                         o.x = *reinterpret_cast<uint32_t *>(&h0);
                         o.y = *reinterpret_cast<uint32_t *>(&h1);
                         o.z = *reinterpret_cast<uint32_t *>(&h2);
@@ -338,7 +336,7 @@ struct EpiG {
                 } else {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
-                        if (col0 + i < c.N) dst[i] = __float2half_rn(v[i] * G_SCALE);
+                        if (col0 + i < c.N) dst[i] = __float2half_rn(acc[ch * 32 + i]);
                 }
             } else {
                 // hi/lo split: g = hi + lo to ~22 bits; planes [hi | lo | hi]
@@ -352,7 +350,7 @@ struct EpiG {
                         uint32_t hi[4], lo[4];
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            const float a = v[i + 2 * j] * G_SCALE, b = v[i + 2 * j + 1] * G_SCALE;
+                            const float a = acc[ch * 32 + i + 2 * j], b = acc[ch * 32 + i + 2 * j + 1];
                             __half2 h = __floats2half2_rn(a, b);
                             float2 hf = __half22float2(h);
                             __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
@@ -369,7 +367,7 @@ struct EpiG {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
                         if (col0 + i < c.N) {
-                            const float a = v[i] * G_SCALE;
+                            const float a = acc[ch * 32 + i];
                             const __half h = __float2half_rn(a);
                             const __half l = __float2half_rn(a - __half2float(h));
                             dst[i] = h;
@@ -387,6 +385,11 @@ struct EpiG {
 // ----------------------------------------------------------------------------
 struct GemmShape {
     int M, N, Kd;
+    // k-blocks (of 64) accumulated inside the tensor core before the partial sum is
+    // moved to fp32 registers and added there with round-to-nearest.  The tensor
+    // core's fp32 accumulation truncates, which biases long K loops (measured:
+    // 1e-4 relative after 6144 MMA steps); short chunks keep it below 1e-6.
+    int chunk_iters;
 };
 
 template <int BLOCK_N>
@@ -429,6 +432,9 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int num_n = (shape.N + BLOCK_N - 1) / BLOCK_N;
     const int num_tiles = num_m * num_n;
     const int k_iters = (shape.Kd + BLOCK_K - 1) / BLOCK_K;
+    const int chunk_iters = (shape.chunk_iters > 0 && shape.chunk_iters < k_iters) ? shape.chunk_iters
+                                                                                   : k_iters;
+    const int n_chunks = (k_iters + chunk_iters - 1) / chunk_iters;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_a);
@@ -476,31 +482,35 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BLOCK_N);
             int stage = 0;
             uint32_t phase = 0;
-            int lt = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
-                const int buf = lt & 1;
-                mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);
-                tcgen05_fence_after();
-                const uint32_t tmem_d = tmem_base + buf * BLOCK_N;
-                for (int kb = 0; kb < k_iters; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
+            uint32_t cc = 0;  // accumulator-chunk counter: buffer = cc & 1
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
+                    const uint32_t buf = cc & 1;
+                    mbar_wait(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
                     tcgen05_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-                    const uint64_t adesc = make_smem_desc(sa);
-                    const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
+                    const uint32_t tmem_d = tmem_base + buf * BLOCK_N;
+                    const int kb0 = ck * chunk_iters;
+                    const int kb1 = min(k_iters, kb0 + chunk_iters);
+                    for (int kb = kb0; kb < kb1; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tcgen05_fence_after();
+                        const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+                        const uint64_t adesc = make_smem_desc(sa);
+                        const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        // +32 bytes per UMMA_K step inside the swizzled 128-byte row
-                        umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
-                                 (uint32_t)((kb | k) != 0));
+                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                            // +32 bytes per UMMA_K step inside the swizzled 128-byte row
+                            umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
+                                     idesc, (uint32_t)((kb > kb0) || (k > 0)));
+                        }
+                        umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
+                        if (++stage == STAGES) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
                     }
-                    umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
-                    if (++stage == STAGES) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
+                    umma_commit(&tfull_bar[buf]);  // this chunk's partial sum is complete
                 }
-                umma_commit(&tfull_bar[buf]);  // accumulator complete
             }
         }
     } else {
@@ -511,21 +521,42 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         c.N = shape.N;
         c.tid = q * 32 + lane;
         c.scratch = epi_scratch;
+        uint32_t cc = 0;
         int lt = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
-            const int buf = lt & 1;
             c.m_blk = t % num_m;
             c.n_blk = t / num_m;
             c.m0 = c.m_blk * BLOCK_M;
             c.n0 = c.n_blk * BLOCK_N;
-            c.buf = buf;
-            c.taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
-            mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
-            tcgen05_fence_after();
-            Epi::template run<BLOCK_N>(ep, c);
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+            c.par = lt & 1;
+            float acc[BLOCK_N];
+            for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
+                const uint32_t buf = cc & 1;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BLOCK_N;
+                mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
+                tcgen05_fence_after();
+                if (ck == 0) {
+#pragma unroll
+                    for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+                        float v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) acc[ch * 32 + i] = v[i];
+                    }
+                } else {
+#pragma unroll
+                    for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+                        float v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) acc[ch * 32 + i] += v[i];
+                    }
+                }
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
+            }
+            Epi::template run<BLOCK_N>(ep, c, acc);
         }
     }
 

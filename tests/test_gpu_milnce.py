@@ -51,6 +51,24 @@ def _check(v, t, dtype, name):
     e_dt = rel_err(dt.cpu().numpy(), ref_dt)
     print(f"{name} {dtype}: loss {e_loss:.2e} den {e_den:.2e} dV {e_dv:.2e} dT {e_dt:.2e}")
     tol = TOL[dtype]
+    if dtype == torch.float32:
+        # float32 arithmetic itself is not 1e-5-accurate once logits reach tens (an absolute
+        # error of 1 ulp(|S|) in S is a relative error of the same size in exp(S)).  Where the
+        # reference's own float32 evaluation (torch port, same GPU) is further than 5e-6 from
+        # float64, allow twice that noise floor instead of the flat 1e-5.
+        vf = vd.clone().requires_grad_(True)
+        tf = td.clone().requires_grad_(True)
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            lf = milnce_oracle.milnce_torch_port(vf, tf)
+            lf.backward()
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
+        floor = max(rel_err(vf.grad.cpu().numpy(), ref_dv), rel_err(tf.grad.cpu().numpy(), ref_dt),
+                    abs(lf.item() - ref_loss) / abs(ref_loss))
+        print(f"    float32 reference-port noise floor on this input: {floor:.2e}")
+        tol = max(tol, 2.0 * floor)
     assert e_loss < tol and e_den < tol and e_dv < tol and e_dt < tol
 
 

@@ -158,5 +158,5 @@ def test_linearity_in_grad_out():
     g1 = torch.rand(256, device="cuda")
     dx1, dy1, _ = sdtw_backward_raw(x, y, g1, 0.1, 0.0, KINDS["cosine"], aux)
     dx2, dy2, _ = sdtw_backward_raw(x, y, 3.0 * g1, 0.1, 0.0, KINDS["cosine"], aux)
-    assert torch.allclose(dx2, 3.0 * dx1, rtol=1e-5, atol=1e-9)
-    assert torch.allclose(dy2, 3.0 * dy1, rtol=1e-5, atol=1e-9)
+    assert ((dx2 - 3.0 * dx1).norm() / dx2.norm()).item() < 1e-6
+    assert ((dy2 - 3.0 * dy1).norm() / dy2.norm()).item() < 1e-6
