@@ -105,6 +105,30 @@ int sdtw_backward(const float *x, const float *y, const float *grad_out,
                   const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
                   void *stream);
 
+/* Forward for callers that cannot allocate device memory at all.  It has no
+ * counterpart in the reference (there the scratch is torch tensors,
+ * soft_dtw_cuda.py:135-136).  Same arguments and results as sdtw_forward, minus
+ * `aux`: the distance matrix and norms that the two forward kernels exchange sit in
+ * a buffer compiled into the library (B200HEAD_SDTW_NOALLOC_MAX_BYTES bytes of
+ * every GPU that loads it, held until exit).  Meant for a binding from a runtime
+ * that owns no device allocator, a process whose pool already holds the whole GPU,
+ * or a loop that must avoid the device-wide stall of cudaMalloc/cudaFree.  The call
+ * performs no cudaMalloc/cudaFree and uses no allocating library.
+ *   - forward only: no aux is produced, so sdtw_backward cannot follow it;
+ *   - limit: align256(4*B*N*M) + align256(4*B*N) + align256(4*B*M) must not exceed
+ *     B200HEAD_SDTW_NOALLOC_MAX_BYTES, else B200HEAD_ERR_WS with the sizes in
+ *     b200head_last_error() (e.g. 256 pairs of 64x64 need 4.3 MiB and fit);
+ *   - the first call on each device looks up the buffer's address for that device
+ *     (the device must be current); make that first call before starting any
+ *     stream capture;
+ *   - the buffer is shared by all calls on a device and is not cleared between
+ *     them (nothing in it needs to start at zero); calls that overlap in time on
+ *     the same GPU race on it, so the caller must serialise them. */
+#define B200HEAD_SDTW_NOALLOC_MAX_BYTES (8u << 20)
+int sdtw_forward_noalloc(const float *x, const float *y, int B, int N, int M, int d,
+                         float gamma, float bandwidth, int dist_kind,
+                         float *R, float *out, void *stream);
+
 /* ------------------------------------------------------------------------
  * Test / diagnostic hooks for the tcgen05 GEMM core (C = alpha * A . B^T with
  * A (M, Kd) and Bm (N, Kd) float16 row-major, C float32 (M, N)).  No

@@ -18,6 +18,7 @@
 //
 // aux layout (caller-allocated, sdtw_aux_bytes): see struct AuxPlan.
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -492,5 +493,109 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
 #undef SDTW_BWD
     B200_LAUNCH_OK("sdtw backward kernels");
     (void)gamma;
+    return 0;
+}
+
+// ----------------------------------------------------------------------------
+// Forward without any allocation by anybody: sdtw_forward_noalloc
+// ----------------------------------------------------------------------------
+// Same kernels as sdtw_forward (dist_kernel + dp_fwd_kernel), but the scratch they
+// need between them - the distance matrix D (B,N,M) and the two norm vectors -
+// lives in the file-scope device array below instead of a caller-provided `aux`.
+// It exists for callers that can hand over input and output pointers but have no
+// way to obtain more device memory: a binding from another runtime that owns no
+// device allocator, a process whose memory pool has already claimed the whole GPU
+// (so a further cudaMalloc would fail), or a latency-critical loop that cannot
+// afford the device-wide synchronisation cudaMalloc/cudaFree imply.
+//
+// The array is part of the library image: every GPU that loads libb200head.so
+// holds these 8 MiB until the process exits, whether or not the entry point is
+// ever called.  All calls on a device share it and it keeps whatever the last
+// call left there.  Nothing in it has to start at zero: every word the wavefront
+// kernel reads was written by the distance kernel of the same call, and the
+// per-cell weights that the backward would need are not produced here at all
+// (forward only).  Two calls that overlap on the same GPU (different streams, or
+// different host threads) would overwrite each other's D - callers must order them.
+namespace {
+
+constexpr size_t NOALLOC_MAX_BYTES = (size_t)B200HEAD_SDTW_NOALLOC_MAX_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_MAX_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+void *g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not an address
+// a kernel may dereference.  The real device address differs per GPU and is looked
+// up once per device, with that device current, through cudaGetSymbolAddress.
+int noalloc_scratch_address(void **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        b200::set_error("sdtw_forward_noalloc: cudaGetDevice failed: %s", cudaGetErrorString(e));
+        return B200HEAD_ERR_CUDA;
+    }
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        b200::set_error("sdtw_forward_noalloc: device ordinal %d not supported (max %d)", dev,
+                        NOALLOC_MAX_DEVICES - 1);
+        return B200HEAD_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_dev_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            b200::set_error("sdtw_forward_noalloc: cudaGetSymbolAddress failed on device %d: %s",
+                            dev, cudaGetErrorString(e));
+            return B200HEAD_ERR_CUDA;
+        }
+        g_noalloc_dev_ptr[dev] = p;
+    }
+    *out = g_noalloc_dev_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int sdtw_forward_noalloc(const float *x, const float *y, int B, int N, int M, int d,
+                                    float gamma, float bandwidth, int dist_kind, float *R,
+                                    float *out, void *stream) {
+    int rc = check_args("sdtw_forward_noalloc", x, y, B, N, M, d, gamma, dist_kind);
+    if (rc) return rc;
+    if (!out) {
+        b200::set_error("sdtw_forward_noalloc: out is null");
+        return B200HEAD_ERR_ARG;
+    }
+    // scratch = D (B,N,M) | ||x|| (B,N) | ||y|| (B,M), each part 256-byte aligned
+    const size_t off_d = 0;
+    const size_t off_nx = align_up(off_d + (size_t)B * N * M * 4, 256);
+    const size_t off_ny = align_up(off_nx + (size_t)B * N * 4, 256);
+    const size_t need = align_up(off_ny + (size_t)B * M * 4, 256);
+    if (need > NOALLOC_MAX_BYTES) {
+        b200::set_error("sdtw_forward_noalloc: B=%d N=%d M=%d needs %zu bytes of scratch but the "
+                        "built-in buffer holds %zu; use sdtw_forward with a caller-allocated aux",
+                        B, N, M, need, NOALLOC_MAX_BYTES);
+        return B200HEAD_ERR_WS;
+    }
+    void *base = nullptr;
+    rc = noalloc_scratch_address(&base);
+    if (rc) return rc;
+    uint8_t *sx = (uint8_t *)base;
+    float *Dm = reinterpret_cast<float *>(sx + off_d);
+    float *nx = reinterpret_cast<float *>(sx + off_nx);
+    float *ny = reinterpret_cast<float *>(sx + off_ny);
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
+    if (dist_kind == B200HEAD_DIST_COSINE)
+        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
+    else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT)
+        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
+    else
+        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
+    B200_LAUNCH_OK("sdtw_forward_noalloc dist_kernel");
+    const int T = std::max(32, (N + 31) / 32 * 32);
+    const size_t sh = 2 * (size_t)(T + 1) * sizeof(double);
+    dp_fwd_kernel<<<B, T, sh, st>>>(Dm, N, M, gamma, bandwidth, R, out, nullptr);
+    B200_LAUNCH_OK("sdtw_forward_noalloc dp_fwd_kernel");
     return 0;
 }
