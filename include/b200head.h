@@ -137,6 +137,10 @@ int sdtw_forward_noalloc(const float *x, const float *y, int B, int N, int M, in
  * ------------------------------------------------------------------------ */
 int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
                          int lda, int ldb, int ldc, float alpha, void *stream);
+/* Same product with A passed transposed: At is (Kd, M) row-major, i.e. the A operand
+ * is read MN-major by the tensor core (the path dtext = G^T . V uses to consume G). */
+int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, int M, int N, int Kd,
+                         int ldat, int ldb, int ldc, float alpha, void *stream);
 
 #ifdef __cplusplus
 }

@@ -36,7 +36,9 @@ struct Scalars {
     float inv_ss;                 // 1 / (s_video * s_text): un-scales S
     float alpha_dvideo;           // grad_loss / (B * 2^13 * s_text)
     float alpha_dtext;            // grad_loss / (B * 2^13 * s_video)
-    float pad;
+    float den_mid_log2;           // (min den + max den) / 2 in the log2 domain
+    int g_fast;                   // 1: den range small enough for the one-exp gradient tile
+    int pad[7];
 };
 
 struct Plan {
@@ -46,6 +48,7 @@ struct Plan {
     long long ld_vk, ld_tk;  // leading dims of the K-major staged operands (cols = P*D)
     long long ld_vt, ld_tt;  // transposed operands: Vt (D, P*B), Tt (D, P*BK)
     long long ld_g, ld_gt;   // G (n, P*BK), Gt (n*K, P*B)
+    long long ld_g2;         // G2 (B, n*K) for the sharded bf16 backward
     int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
     int chunk_s, chunk_g;    // k-blocks per tensor-core accumulation chunk (S passes / grad GEMMs)
     size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_g, off_gt, total;
@@ -66,7 +69,7 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.ld_tt = (long long)align_up((size_t)p.P * p.BK, 8);
     p.ld_g = p.ld_tt;
     p.ld_gt = p.ld_vt;
-    p.nb_r = (int)((p.BK + BLOCK_N - 1) / BLOCK_N);
+    p.nb_r = 2 * (int)((p.BK + BLOCK_N - 1) / BLOCK_N);  // one row partial per 64-column half tile
     p.nb_c = (B + BLOCK_N - 1) / BLOCK_N;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 1024); return r; };
@@ -77,9 +80,12 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.off_tt = take((size_t)D * p.ld_tt * 2);
     p.off_pr = take((size_t)p.nb_r * n * 4);
     p.off_pc = take((size_t)p.nb_c * n * K * 4);
-    p.off_diff = take((size_t)n * 4);
+    p.off_diff = take((size_t)n * 4 * 2);  // den - nom, then the merged den
     p.off_g = take((size_t)n * p.ld_g * 2);
-    p.off_gt = take((size_t)n * K * p.ld_gt * 2);
+    // P == 3: G^T (n*K, P*B) from the transposed pass.  P == 1: G2 = G[all rows, own columns]
+    // (B, n*K), read MN-major by the dtext GEMM; not needed at all when n == B.
+    p.ld_g2 = (long long)align_up((size_t)n * K, 8);
+    p.off_gt = take(std::max((size_t)n * K * p.ld_gt * 2, (size_t)B * p.ld_g2 * 2));
     p.total = o;
     return true;
 }
@@ -123,10 +129,37 @@ __global__ void scalars_forward_kernel(Scalars *s) {
     s->inv_ss = (1.f / sv) * (1.f / st);
 }
 
-__global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, int B) {
-    const float g = grad_loss[0] / ((float)B * tc::G_SCALE);
-    s->alpha_dvideo = g / s->s_text;
-    s->alpha_dtext = g / s->s_video;
+// one block: gradient scales + the range of den (decides the one-exp path of EpiG)
+__global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, const float *den, int B) {
+    __shared__ float smin[32], smax[32];
+    float lo = INFINITY, hi = -INFINITY;
+    for (int i = threadIdx.x; i < B; i += blockDim.x) {
+        const float d = den[i];
+        lo = fminf(lo, d);
+        hi = fmaxf(hi, d);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        smin[threadIdx.x >> 5] = lo;
+        smax[threadIdx.x >> 5] = hi;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) {
+            lo = fminf(lo, smin[w]);
+            hi = fmaxf(hi, smax[w]);
+        }
+        const float g = grad_loss[0] / ((float)B * tc::G_SCALE);
+        s->alpha_dvideo = g / s->s_text;
+        s->alpha_dtext = g / s->s_video;
+        // finite and within 60 nats: 2^(den_i - den_j) and its two factors stay in fp32 range
+        const bool ok = (hi - lo) < 60.f && isfinite(hi) && isfinite(lo);
+        s->g_fast = ok ? 1 : 0;
+        s->den_mid_log2 = ok ? 0.5f * (lo + hi) * tc::LOG2E : 0.f;
+    }
 }
 
 // Plane order along K.  A-side [hi | lo | hi], B-side [hi | hi | lo]:
@@ -182,34 +215,54 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// merge the per-tile partial log-sum-exps of 32 samples per block: lane = sample (coalesced
+// reads), the block's 8 warps stride over the partials, then combine through smem.
+//   part_r[t][w], t < nb_r          -> row_i = lse over all text columns
+//   part_c[t][w*K + k], t < nb_c    -> col_i = lse over all video rows and the K candidates
+__global__ void __launch_bounds__(256)
+merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict__ part_c, int K, int n,
+                      int nb_r, int nb_c, float *__restrict__ rowcol) {
+    __shared__ float sm[8][32], ss[8][32];
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    const int w = blockIdx.x * 32 + lane;
+    float m = -INFINITY, s = 0.f;
+    auto push = [&](float v) {
+        if (v > m) {
+            s = s * __expf(m - v) + 1.f;  // m = -inf at the start: exp(-inf) = 0
+            m = v;
+        } else if (v > -INFINITY) {
+            s += __expf(v - m);
+        }
+    };
+    if (w < n) {
+        for (int t = wp; t < nb_r; t += 8) push(part_r[(size_t)t * n + w]);
+        const size_t nk = (size_t)n * K;
+        for (int t = wp; t < nb_c; t += 8)
+            for (int k = 0; k < K; ++k) push(part_c[(size_t)t * nk + (size_t)w * K + k]);
+    }
+    sm[wp][lane] = m;
+    ss[wp][lane] = s;
+    __syncthreads();
+    if (wp == 0 && w < n) {
+        float mm = sm[0][lane];
+        for (int j = 1; j < 8; ++j) mm = fmaxf(mm, sm[j][lane]);
+        float tot = 0.f;
+        for (int j = 0; j < 8; ++j)
+            if (sm[j][lane] > -INFINITY) tot += ss[j][lane] * __expf(sm[j][lane] - mm);
+        rowcol[w] = mm + logf(tot);  // = logaddexp(row_i, col_i) = den_i  (loss.py:16-17)
+    }
+}
+
+// warp per owned sample: positives from exact fp32 dot products (loss.py:13-15), den, den - nom
 template <typename T>
 __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict__ text,
-                                const float *__restrict__ part_r, const float *__restrict__ part_c,
-                                int B, int K, int D, int i0, int n, int nb_r, int nb_c,
+                                const float *__restrict__ rowcol, int K, int D, int i0, int n,
                                 float *__restrict__ den, float *__restrict__ nom,
                                 float *__restrict__ diff) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (w >= n) return;
     const int i = i0 + w;
-    // row statistic: lse over the n-blocks of pass R
-    float m = -INFINITY;
-    for (int t = lane; t < nb_r; t += 32) m = fmaxf(m, part_r[(size_t)t * n + w]);
-    m = warp_max(m);
-    float s = 0.f;
-    for (int t = lane; t < nb_r; t += 32) s += expf(part_r[(size_t)t * n + w] - m);
-    const float row = m + logf(warp_sum(s));
-    // column statistic: lse over the n-blocks of pass C and the K candidates of sample i
-    const int nk = n * K;
-    m = -INFINITY;
-    for (int t = lane; t < nb_c * K; t += 32)
-        m = fmaxf(m, part_c[(size_t)(t / K) * nk + (size_t)w * K + (t % K)]);
-    m = warp_max(m);
-    s = 0.f;
-    for (int t = lane; t < nb_c * K; t += 32)
-        s += expf(part_c[(size_t)(t / K) * nk + (size_t)w * K + (t % K)] - m);
-    const float col = m + logf(warp_sum(s));
-    // positives: exact fp32 dot products <v_i, t_{iK+k}>  (loss.py:13-15)
     float pm = -INFINITY, ps = 0.f;
     const T *v = video + (size_t)i * D;
     for (int k = 0; k < K; ++k) {
@@ -224,10 +277,9 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
             ps += expf(acc - pm);
         }
     }
-    const float nm = pm + logf(ps);
-    const float hi = fmaxf(row, col), lo = fminf(row, col);
-    const float dn = hi + log1pf(expf(lo - hi));
     if (lane == 0) {
+        const float nm = pm + logf(ps);
+        const float dn = rowcol[w];
         den[i] = dn;
         nom[i] = nm;
         diff[w] = dn - nm;
@@ -263,17 +315,21 @@ int num_sms() {
     return sms > 0 ? sms : 148;
 }
 
-template <class Epi>
+// A_MN = false: A is (M, Kd) with leading dimension lda.
+// A_MN = true : A is passed transposed, (Kd, M) with leading dimension lda (MN-major operand).
+template <class Epi, bool A_MN = false>
 int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                 int chunk_iters, const typename Epi::Params &ep, cudaStream_t stream,
                 const char *what) {
-    using L = tc::SmemLayout<BLOCK_N>;
+    using L = tc::SmemLayout<BLOCK_N, Epi::STAGE_BYTES>;
     CUtensorMap ma, mb;
-    int rc = b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda, tc::BLOCK_M);
+    int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
+                  : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
+                                           tc::BLOCK_M);
     if (rc) return rc;
     rc = b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, BLOCK_N);
     if (rc) return rc;
-    auto kern = tc::gemm_tn_kernel<BLOCK_N, Epi>;
+    auto kern = tc::gemm_tn_kernel<BLOCK_N, Epi, A_MN>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int tiles = ((M + tc::BLOCK_M - 1) / tc::BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
@@ -333,19 +389,29 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
     float *diff = reinterpret_cast<float *>(ws + p.off_diff);
     const int Kd = p.P * p.D;
-    // pass R: rows = owned video rows, columns = all text rows
-    tc::EpiRowLse::Params er{pr, (long long)p.n, &sc->inv_ss};
-    rc = launch_gemm<tc::EpiRowLse>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n,
-                                    (int)p.BK, Kd, p.chunk_s, er, st, "milnce forward pass R");
-    if (rc) return rc;
-    // pass C: rows = owned text rows, columns = all video rows
-    tc::EpiRowLse::Params ec{pc, (long long)p.n * p.K, &sc->inv_ss};
-    rc = launch_gemm<tc::EpiRowLse>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk,
-                                    p.n * p.K, p.B, Kd, p.chunk_s, ec, st, "milnce forward pass C");
-    if (rc) return rc;
+    float *rowcol = diff + p.n;
+    if (p.n == p.B) {
+        // one pass over S: row statistic per thread, column statistic by a cross-lane reduction
+        tc::EpiRowCol::Params e{pr, (long long)p.n, pc, (long long)p.BK, &sc->inv_ss};
+        rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd, p.chunk_s, e, st,
+                                        "milnce forward (fused row+column statistics)");
+        if (rc) return rc;
+    } else {
+        // sharded: rows [i0, i0+n) x all columns -> row statistic of the owned samples
+        tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, &sc->inv_ss};
+        rc = launch_gemm<tc::EpiRowCol>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n,
+                                        (int)p.BK, Kd, p.chunk_s, er, st, "milnce forward row block");
+        if (rc) return rc;
+        // all rows x columns of the owned samples -> their column statistic
+        tc::EpiRowCol::Params ec{nullptr, 0, pc, (long long)p.n * p.K, &sc->inv_ss};
+        rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
+                                        p.n * p.K, Kd, p.chunk_s, ec, st, "milnce forward column block");
+        if (rc) return rc;
+    }
+    merge_partials_kernel<<<(p.n + 31) / 32, 256, 0, st>>>(pr, pc, p.K, p.n, p.nb_r, p.nb_c, rowcol);
     const int warps_per_block = 8;
     finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
-        video, text, pr, pc, p.B, p.K, p.D, p.i0, p.n, p.nb_r, p.nb_c, den, nom, diff);
+        video, text, rowcol, p.K, p.D, p.i0, p.n, den, nom, diff);
     loss_reduce_kernel<<<1, 1024, 0, st>>>(diff, p.n, p.B, loss);
     B200_LAUNCH_OK("milnce finalize");
     return 0;
@@ -361,7 +427,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    scalars_backward_kernel<<<1, 1, 0, st>>>(sc, grad_loss, p.B);
+    scalars_backward_kernel<<<1, 1024, 0, st>>>(sc, grad_loss, den, p.B);
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
@@ -369,23 +435,44 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     __half *gt = reinterpret_cast<__half *>(ws + p.off_gt);
     const int Kd = p.P * p.D;
-    // pass R: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
-    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, p.K, &sc->inv_ss};
+    const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
+    // row block: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, 0, p.K, &sc->inv_ss, fast};
     rc = launch_gemm<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
-                               p.chunk_s, gr, st, "milnce backward pass R");
-    if (rc) return rc;
-    // pass C: G^T (n*K, B): row r <-> sample (i0*K + r) / K, column <-> sample index itself
-    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, p.K, 1, &sc->inv_ss};
-    rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
-                               p.B, Kd, p.chunk_s, gc, st, "milnce backward pass C");
+                               p.chunk_s, gr, st, "milnce backward row block");
     if (rc) return rc;
     // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
     rc = launch_gemm<tc::EpiStore>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)(p.P * p.BK), p.chunk_g,
                                    sv, st, "milnce dvideo GEMM");
     if (rc) return rc;
-    // dtext (n*K, D) = G^T . V   : A = Gt (n*K, P*B), Bm = Vt (D, P*B)
     tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext};
+    if (p.P == 1) {
+        // dtext (n*K, D) = G[:, own columns]^T . V, reading G as an MN-major A operand:
+        // nobody materialises G^T.  On one GPU (n == B) the G of the row block is the G needed.
+        const __half *g2 = g;
+        long long ld_g2 = p.ld_g;
+        if (p.n != p.B) {
+            // column block: G2 (B, n*K): row <-> sample r, column c <-> sample (i0*K + c) / K
+            tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, 1, p.i0 * p.K, p.K,
+                                &sc->inv_ss, fast};
+            rc = launch_gemm<tc::EpiG>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
+                                       p.n * p.K, Kd, p.chunk_s, gc, st, "milnce backward column block");
+            if (rc) return rc;
+            g2 = gt;
+            ld_g2 = p.ld_g2;
+        }
+        rc = launch_gemm<tc::EpiStore, true>(g2, ld_g2, vt, p.ld_vt, p.n * p.K, p.D, p.B, p.chunk_g, sd,
+                                             st, "milnce dtext GEMM (MN-major G)");
+        return rc;
+    }
+    // fp32 inputs (hi/lo planes): the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
+    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, p.K, 0, 1, &sc->inv_ss,
+                        fast};
+    rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
+                               p.B, Kd, p.chunk_s, gc, st, "milnce backward transposed block");
+    if (rc) return rc;
+    // dtext (n*K, D) = G^T . V   : A = Gt (n*K, P*B), Bm = Vt (D, P*B)
     rc = launch_gemm<tc::EpiStore>(gt, p.ld_gt, vt, p.ld_vt, p.n * p.K, p.D, p.P * p.B, p.chunk_g, sd, st,
                                    "milnce dtext GEMM");
     return rc;
@@ -463,4 +550,17 @@ extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
     return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                      "gemm_tn_f16 test hook");
+}
+
+extern "C" int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, int M, int N, int Kd,
+                                    int ldat, int ldb, int ldc, float alpha, void *stream) {
+    if (!At || !Bm || !C || M <= 0 || N <= 0 || Kd <= 0) {
+        b200::set_error("b200head_gemm_at_f16: bad argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    return launch_gemm<tc::EpiStore, true>(At, ldat, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
+                                           "gemm_at_f16 test hook");
 }

@@ -2,11 +2,12 @@
 //
 //   C[m, n] = sum_k A[m, k] * Bm[n, k]        A (M, Kd), Bm (N, Kd) fp16, K-major
 //
-// One persistent CTA per SM, 192 threads:
+// One persistent CTA per SM, 320 threads:
 //   warp 0      TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring)
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
-//   warps 2..5  epilogue: tcgen05.ld the fp32 accumulator (one TMEM lane = one
-//               output row per thread) into registers, then run the epilogue functor
+//   warps 2..9  epilogue: tcgen05.ld the fp32 accumulator (one TMEM lane = one output
+//               row, half the tile's columns per thread) into registers, then run the
+//               epilogue functor
 // Accumulators are double-buffered in TMEM (2 x BLOCK_N columns) and drained to
 // registers per K-chunk, so the epilogue of tile t overlaps the MMAs of tile t+1
 // and long K loops are summed in fp32 registers (round-to-nearest) rather than
@@ -26,8 +27,6 @@ namespace tc {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // fp16 elements = 128 bytes = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
-constexpr int NUM_EPI_THREADS = 128;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -89,9 +88,7 @@ __device__ __forceinline__ void tcgen05_fence_before() {
 __device__ __forceinline__ void tcgen05_fence_after() {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
-__device__ __forceinline__ void epi_bar_sync() {  // named barrier 1: the 128 epilogue threads
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-}
+__device__ __forceinline__ void epi_bar_sync();  // named barrier over the epilogue threads
 
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar,
                                             int c0, int c1) {
@@ -128,9 +125,25 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
     return d;
 }
-// kind::f16 instruction descriptor: fp16 x fp16 -> fp32, both operands K-major.
-__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
-    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+// MN-major operand tile (the M/N index is the contiguous one): the tile is stored
+// as 64-element-wide slabs, each slab = BLOCK_K rows (K index) of 128 bytes,
+// SWIZZLE_128B.  Canonical layout ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units:
+// LBO = distance between slabs (next 64 M/N elements), SBO = distance between
+// 8-row K groups (1024 B).  `lbo_bytes` is the slab size.
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// kind::f16 instruction descriptor: fp16 x fp16 -> fp32; a_mn = 1 selects an
+// MN-major A operand (bit 15), B is always K-major here.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int a_mn = 0) {
+    return (1u << 4) | ((uint32_t)a_mn << 15) | ((uint32_t)(n >> 3) << 17) |
+           ((uint32_t)(m >> 4) << 24);
 }
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                          uint32_t idesc, uint32_t accumulate) {
@@ -179,34 +192,44 @@ __device__ __forceinline__ float fast_exp2(float x) {
 // ----------------------------------------------------------------------------
 // Epilogue context handed to the functors
 // ----------------------------------------------------------------------------
+// Eight epilogue warps: warp (q, h) owns TMEM lanes [32q, 32q+32) (= 32 output rows)
+// and the column half h of the tile, i.e. HN = BLOCK_N/2 columns per thread.
 struct EpiCtx {
-    int m0, n0;        // tile origin
+    int m0, n0;        // origin of this thread's sub-tile: row block start, FIRST COLUMN OF ITS HALF
     int m_blk, n_blk;  // tile coordinates
+    int half;          // 0 / 1: which column half
     int M, N;          // problem extent
-    int tid;           // 0..127 within the epilogue warps; row in tile = tid
+    int tid;           // row within the tile, 0..127
+    int etid;          // 0..255 within the epilogue warps
+    int lane, q;       // lane, lane quarter
     int par;           // tile parity, for double-buffered smem scratch
-    float *scratch;    // 2 * BLOCK_N floats of smem private to the epilogue warps
+    float *scratch;    // SCRATCH_FLOATS floats of smem shared by the epilogue warps
+    uint8_t *stage;    // Epi::STAGE_BYTES bytes of smem (this warp's slice starts at warp_slot)
+    int warp_slot;     // 0..7
 };
-// Every functor receives the finished fp32 accumulator row of its thread in
-// registers (acc[BLOCK_N], compile-time indexed): the kernel has already drained
-// TMEM, so the tensor core is working on the next tile while the functor runs.
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
+// Every functor receives the finished fp32 accumulator (its row, its column half) in
+// registers (acc[HN], compile-time indexed): the kernel has already drained TMEM, so
+// the tensor core is working on the next tile while the functor runs.
 
 // ---- plain store: C = alpha * acc (dvideo / dtext GEMMs, and the test hook) ----
 struct EpiStore {
+    static constexpr int STAGE_BYTES = 0;
     struct Params {
         float *C;
         long long ldc;
         float alpha;
         const float *alpha_dev;  // optional device scalar multiplied into alpha
     };
-    template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
+    template <int HN>
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
         float alpha = p.alpha;
         if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
         const int row = c.m0 + c.tid;
         if (row >= c.M) return;
 #pragma unroll
-        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+        for (int ch = 0; ch < HN / 32; ++ch) {
             const int col0 = c.n0 + ch * 32;
             if (col0 >= c.N) break;
             float *dst = p.C + (long long)row * p.ldc + col0;
@@ -227,44 +250,152 @@ struct EpiStore {
     }
 };
 
-// ---- row log-sum-exp of the tile (MIL-NCE forward; reference loss.py:16-17) ----
-// part[n_blk][row] = log sum_{n in tile} exp(scale * acc[row, n])      (natural log)
-struct EpiRowLse {
+// ---- row AND column log-sum-exp of the tile (MIL-NCE forward; loss.py:16-17) ----
+// part_row[2*n_blk + half][row] = log sum_{n in half tile} exp(s[row, n])     s = scale * acc
+// part_col[m_blk][col]          = log sum_{m in tile} exp(s[m, col])          (natural logs)
+// One exp per element serves both statistics: e = 2^(y - wmax) with wmax the maximum over
+// the warp's 32 x HN sub-tile.  Row sums are thread-local; column sums need a reduction
+// across the 32 lanes, done with a transposing butterfly (31 shuffles per 32 columns).
+// A row or column whose sum underflows under the shared shift (everything in it more than
+// 2^100 below wmax) is recomputed exactly with its own maximum - rare, so the common case
+// pays nothing for arbitrary logit ranges (embeddings are not normalised).
+template <int H>
+__device__ __forceinline__ void bfly_step(float (&a)[32], int lane) {
+    const bool up = (lane & H) != 0;
+#pragma unroll
+    for (int j = 0; j < H; ++j) {
+        const float send = up ? a[j] : a[j + H];
+        const float keep = up ? a[j + H] : a[j];
+        a[j] = keep + __shfl_xor_sync(0xffffffffu, send, H);
+    }
+}
+__device__ __forceinline__ float warp_max_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+constexpr float TINY_SUM = 7.8886090522101181e-31f;  // 2^-100
+
+struct EpiRowCol {
+    static constexpr int STAGE_BYTES = 0;
     struct Params {
-        float *part;
-        long long ldp;           // rows per n-block slab
-        const float *scale_dev;  // device scalar: un-does the fp16 staging scale
+        float *part_row;  // may be null: skip the row statistic
+        long long ldr;
+        float *part_col;  // may be null: skip the column statistic
+        long long ldc;
+        const float *scale_dev;
     };
-    template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
-        const float sc = __ldg(p.scale_dev) * LOG2E;  // work in the log2 domain
-        float mx = -INFINITY;
-#pragma unroll
-        for (int i = 0; i < BLOCK_N; ++i) {
-            acc[i] = (c.n0 + i < c.N) ? acc[i] * sc : -INFINITY;
-            mx = fmaxf(mx, acc[i]);
-        }
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll
-        for (int i = 0; i < BLOCK_N; i += 4) {
-            s0 += fast_exp2(acc[i] - mx);
-            s1 += fast_exp2(acc[i + 1] - mx);
-            s2 += fast_exp2(acc[i + 2] - mx);
-            s3 += fast_exp2(acc[i + 3] - mx);
-        }
+    template <int HN>
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
+        static_assert(HN == 64, "scratch layout assumes 128-wide tiles");
+        const float sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        const int lane = c.lane;
         const int row = c.m0 + c.tid;
-        if (row < c.M)
-            p.part[(long long)c.n_blk * p.ldp + row] = (mx + log2f((s0 + s1) + (s2 + s3))) * LN2;
+        const bool row_ok = row < c.M;
+        const bool want_col = (p.part_col != nullptr);
+        if (c.n0 + HN > c.N) {  // ragged right edge (warp-uniform): mask the columns past N
+#pragma unroll
+            for (int i = 0; i < HN; ++i)
+                if (c.n0 + i >= c.N) acc[i] = -INFINITY;
+        }
+        float tmax = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < HN; ++i) tmax = fmaxf(tmax, acc[i]);
+        tmax *= sc;  // sc > 0
+        const float wmax = warp_max_f(row_ok ? tmax : -INFINITY);
+        float wl[HN / 32];
+        float row_lse = -INFINITY;
+        if (wmax > -INFINITY) {  // warp-uniform; false only for fully masked sub-tiles
+            float rs = 0.f;
+#pragma unroll
+            for (int ch = 0; ch < HN / 32; ++ch) {
+                float a[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    a[j] = row_ok ? fast_exp2(fmaf(acc[ch * 32 + j], sc, -wmax)) : 0.f;
+                    rs += a[j];
+                }
+                wl[ch] = -INFINITY;
+                if (want_col) {
+                    bfly_step<16>(a, lane);
+                    bfly_step<8>(a, lane);
+                    bfly_step<4>(a, lane);
+                    bfly_step<2>(a, lane);
+                    bfly_step<1>(a, lane);
+                    const float cs = a[0];
+                    wl[ch] = wmax + log2f(cs);
+                    const bool valid_col = (c.n0 + ch * 32 + lane) < c.N;
+                    if (__any_sync(0xffffffffu, valid_col && cs < TINY_SUM)) {
+                        // exact per-column path for this 32x32 block
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float y = row_ok ? acc[ch * 32 + j] * sc : -INFINITY;
+                            const float cm = warp_max_f(y);
+                            const float e = (cm > -INFINITY) ? fast_exp2(y - cm) : 0.f;
+                            const float s = warp_sum_f(e);
+                            if (lane == j) wl[ch] = cm + log2f(s);
+                        }
+                    }
+                }
+            }
+            row_lse = wmax + log2f(rs);
+            if (rs < TINY_SUM && tmax > -INFINITY) {  // exact per-row path
+                float r2 = 0.f;
+#pragma unroll
+                for (int i = 0; i < HN; ++i) r2 += fast_exp2(fmaf(acc[i], sc, -tmax));
+                row_lse = tmax + log2f(r2);
+            }
+        } else {
+#pragma unroll
+            for (int ch = 0; ch < HN / 32; ++ch) wl[ch] = -INFINITY;
+        }
+        if (p.part_row != nullptr && row_ok)
+            p.part_row[(long long)(c.n_blk * 2 + c.half) * p.ldr + row] = row_lse * LN2;
+        if (want_col) {
+            // merge the four lane-quarters' partials through smem (double-buffered by tile parity)
+            float *buf = c.scratch + c.par * (4 * 128);
+#pragma unroll
+            for (int ch = 0; ch < HN / 32; ++ch)
+                buf[c.q * 128 + c.half * HN + ch * 32 + lane] = wl[ch];
+            epi_bar_sync();
+            if (c.etid < 128) {
+                const float v0 = buf[c.etid], v1 = buf[128 + c.etid], v2 = buf[256 + c.etid],
+                            v3 = buf[384 + c.etid];
+                const float m = fmaxf(fmaxf(v0, v1), fmaxf(v2, v3));
+                float out = -INFINITY;
+                if (m > -INFINITY)
+                    out = (m + log2f(fast_exp2(v0 - m) + fast_exp2(v1 - m) + fast_exp2(v2 - m) +
+                                     fast_exp2(v3 - m))) * LN2;
+                const int col = c.n_blk * 128 + c.etid;
+                if (col < c.N) p.part_col[(long long)c.m_blk * p.ldc + col] = out;
+            }
+        }
     }
 };
 
 // ---- softmax-gradient tile (MIL-NCE backward; autograd of loss.py:11-18) ----
 // G[r, n] = 2^13 * ( e^{s - den[rs]} + e^{s - den[cs]} - [rs == cs] e^{s - nom[rs]} ),
-// s = scale * acc, rs = (row_off + r) / rdiv, cs = n / cdiv the sample indices of the
-// row and the column.  Written as fp16 (planes == 1) or as hi/lo fp16 planes laid
+// s = scale * acc, rs = (row_off + r) / rdiv, cs = (col_off + n) / cdiv the sample indices
+// of the row and the column.  Written as fp16 (planes == 1) or as hi/lo fp16 planes laid
 // out [hi | lo | hi] along the row (planes == 3) for the fp32-accurate path.
+// Fast path (den range < 60 nats, decided once per call on the device): one exp per
+// element, e^{s-den_r} (1 + 2^{den_r - mid} 2^{mid - den_c}); otherwise two exps.
+// The fp16 sub-tile of a warp (32 rows x 64 columns) is staged in that warp's 4 KB of
+// shared memory (XOR-swizzled 16-byte chunks, conflict-free) and written out as full
+// 128-byte row segments; row-per-thread stores straight from registers left half-filled
+// 32-byte sectors 64 KB apart and ran the G pass at under 1 TB/s.
 constexpr float G_SCALE = 8192.f;
+struct GFast {
+    const int *flag_dev;
+    const float *mid_log2_dev;
+};
 struct EpiG {
+    static constexpr int STAGE_BYTES = NUM_EPI_WARPS * 32 * 64 * 2;  // 32 KB
     struct Params {
         const float *den;  // all B entries
         const float *nom;
@@ -272,110 +403,122 @@ struct EpiG {
         long long ldo;
         long long plane_stride;  // = N (columns per plane)
         int planes;              // 1 or 3
-        int row_off, rdiv, cdiv;
+        int row_off, rdiv, col_off, cdiv;
         const float *scale_dev;
+        GFast fast;
     };
-    template <int BLOCK_N>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[BLOCK_N]) {
-        static_assert(BLOCK_N <= NUM_EPI_THREADS, "one table entry per epilogue thread");
-        float *tab = c.scratch + c.par * BLOCK_N;  // den of the column's sample, log2 domain
-        if (c.tid < BLOCK_N) {
-            const int n = c.n0 + c.tid;
-            tab[c.tid] = (n < c.N) ? __ldg(p.den + n / p.cdiv) * LOG2E : INFINITY;
+    // write this warp's 32 x 64 fp16 sub-tile held in `vals` (already scaled) to dst planes
+    template <int HN>
+    __device__ static void store_plane(const EpiCtx &c, uint8_t *wstage, const uint32_t (&packed)[HN / 2],
+                                       __half *out, long long ldo) {
+        // stage: row r = lane, 8 chunks of 16 B (8 halves); chunk k stored at k ^ (r & 7)
+        const int r = c.lane;
+#pragma unroll
+        for (int k = 0; k < HN / 8; ++k) {
+            uint4 v = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
+            *reinterpret_cast<uint4 *>(wstage + r * 128 + ((k ^ (r & 7)) << 4)) = v;
+        }
+        __syncwarp();
+        // write-out: each instruction covers 4 rows x 128 B; lane -> (row = it*4 + lane/8, chunk = lane%8)
+        const int sub = c.lane >> 3, k = c.lane & 7;
+        const int col = c.n0 + k * 8;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + sub;
+            const int grow = c.m0 + c.q * 32 + rr;
+            const uint4 v = *reinterpret_cast<const uint4 *>(wstage + rr * 128 + ((k ^ (rr & 7)) << 4));
+            if (grow < c.M) {
+                __half *dst = out + (long long)grow * ldo + col;
+                if (col + 8 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
+                    *reinterpret_cast<uint4 *>(dst) = v;
+                } else {
+                    const __half *hv = reinterpret_cast<const __half *>(&v);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e)
+                        if (col + e < c.N) dst[e] = hv[e];
+                }
+            }
+        }
+        __syncwarp();
+    }
+    template <int HN>
+    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
+        static_assert(HN == 64, "staging layout assumes 64 columns per warp");
+        const bool fast = __ldg(p.fast.flag_dev) != 0;
+        const float mid = __ldg(p.fast.mid_log2_dev);
+        float *tab = c.scratch + c.par * 128;  // per column of the 128-wide tile
+        if (c.etid < 128) {
+            const int n = c.n_blk * 128 + c.etid;
+            float t;
+            if (n < c.N) {
+                const float dc = __ldg(p.den + (p.col_off + n) / p.cdiv) * LOG2E;
+                t = fast ? fast_exp2(mid - dc) : dc;  // fast: column factor 2^(mid - den_c)
+            } else {
+                t = fast ? 0.f : INFINITY;  // masked column (never stored)
+            }
+            tab[c.etid] = t;
         }
         epi_bar_sync();
+        tab += c.half * HN;
         const float sc = __ldg(p.scale_dev) * LOG2E;
         const int row = c.m0 + c.tid;
         const int rs = (p.row_off + min(row, c.M - 1)) / p.rdiv;
         const float dr = __ldg(p.den + rs) * LOG2E;
         const float nr = __ldg(p.nom + rs) * LOG2E;
-        // does this tile touch the positives (row sample == column sample)?
+        const float dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
+        const float ar = fast ? fast_exp2(dr - mid) : 0.f;
+        // does this half tile touch the positives (row sample == column sample)?
         const int rs_lo = (p.row_off + c.m0) / p.rdiv;
         const int rs_hi = (p.row_off + min(c.m0 + BLOCK_M, c.M) - 1) / p.rdiv;
-        const int cs_lo = c.n0 / p.cdiv;
-        const int cs_hi = (min(c.n0 + BLOCK_N, c.N) - 1) / p.cdiv;
-        const bool diag_tile = !(rs_hi < cs_lo || cs_hi < rs_lo);
+        const int cs_lo = (p.col_off + c.n0) / p.cdiv;
+        const int cs_hi = (p.col_off + min(c.n0 + HN, c.N) - 1) / p.cdiv;
+        const bool diag_tile = (c.n0 < c.N) && !(rs_hi < cs_lo || cs_hi < rs_lo);
         if (!diag_tile) {
+            if (fast) {
 #pragma unroll
-            for (int i = 0; i < BLOCK_N; ++i) {
-                const float y = acc[i] * sc;
-                acc[i] = (fast_exp2(y - dr) + fast_exp2(y - tab[i])) * G_SCALE;
+                for (int i = 0; i < HN; ++i) {
+                    const float e = fast_exp2(fmaf(acc[i], sc, -dr13));
+                    acc[i] = fmaf(e, ar * tab[i], e);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < HN; ++i) {
+                    const float y = acc[i] * sc;
+                    acc[i] = (fast_exp2(y - dr) + fast_exp2(y - tab[i])) * G_SCALE;
+                }
             }
         } else {
 #pragma unroll
-            for (int i = 0; i < BLOCK_N; ++i) {
+            for (int i = 0; i < HN; ++i) {
                 const float y = acc[i] * sc;
-                float g = fast_exp2(y - dr) + fast_exp2(y - tab[i]);
-                if ((c.n0 + i) / p.cdiv == rs) g -= fast_exp2(y - nr);  // the positives
+                const int cs = (p.col_off + c.n0 + i) / p.cdiv;
+                const float dc = (c.n0 + i < c.N) ? __ldg(p.den + cs) * LOG2E : INFINITY;
+                float g = fast_exp2(y - dr) + fast_exp2(y - dc);
+                if (cs == rs) g -= fast_exp2(y - nr);  // the positives
                 acc[i] = g * G_SCALE;
             }
         }
-        if (row >= c.M) return;
+        if (c.n0 >= c.N) return;  // warp-uniform: nothing of this half is inside the matrix
+        uint8_t *wstage = c.stage + c.warp_slot * (32 * 64 * 2);
+        uint32_t hi[HN / 2];
 #pragma unroll
-        for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
-            const int col0 = c.n0 + ch * 32;
-            if (col0 >= c.N) break;
-            __half *dst = p.out + (long long)row * p.ldo + col0;
-            const bool full = (col0 + 32 <= c.N);
-            if (p.planes == 1) {
-                if (full && ((((uintptr_t)dst) & 15) == 0)) {
+        for (int i = 0; i < HN / 2; ++i) {
+            __half2 h = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+            hi[i] = *reinterpret_cast<uint32_t *>(&h);
+        }
+        store_plane<HN>(c, wstage, hi, p.out, p.ldo);
+        if (p.planes == 3) {
+            // hi/lo split: g = hi + lo to ~22 bits; planes [hi | lo | hi]
+            store_plane<HN>(c, wstage, hi, p.out + 2 * p.plane_stride, p.ldo);
+            uint32_t lo[HN / 2];
 #pragma unroll
-                    for (int i = 0; i < 32; i += 8) {
-                        const int e = ch * 32 + i;
-                        __half2 h0 = __floats2half2_rn(acc[e], acc[e + 1]);
-                        __half2 h1 = __floats2half2_rn(acc[e + 2], acc[e + 3]);
-                        __half2 h2 = __floats2half2_rn(acc[e + 4], acc[e + 5]);
-                        __half2 h3 = __floats2half2_rn(acc[e + 6], acc[e + 7]);
-                        uint4 o;
-                        o.x = *reinterpret_cast<uint32_t *>(&h0);
-                        o.y = *reinterpret_cast<uint32_t *>(&h1);
-                        o.z = *reinterpret_cast<uint32_t *>(&h2);
-                        o.w = *reinterpret_cast<uint32_t *>(&h3);
-                        *reinterpret_cast<uint4 *>(dst + i) = o;
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (col0 + i < c.N) dst[i] = __float2half_rn(acc[ch * 32 + i]);
-                }
-            } else {
-                // hi/lo split: g = hi + lo to ~22 bits; planes [hi | lo | hi]
-                __half *d_lo = dst + p.plane_stride;
-                __half *d_h2 = dst + 2 * p.plane_stride;
-                const bool al = full && ((((uintptr_t)dst) & 15) == 0) &&
-                                ((((uintptr_t)d_lo) & 15) == 0) && ((((uintptr_t)d_h2) & 15) == 0);
-                if (al) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 8) {
-                        uint32_t hi[4], lo[4];
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const float a = acc[ch * 32 + i + 2 * j], b = acc[ch * 32 + i + 2 * j + 1];
-                            __half2 h = __floats2half2_rn(a, b);
-                            float2 hf = __half22float2(h);
-                            __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
-                            hi[j] = *reinterpret_cast<uint32_t *>(&h);
-                            lo[j] = *reinterpret_cast<uint32_t *>(&l);
-                        }
-                        uint4 oh = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                        uint4 ol = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                        *reinterpret_cast<uint4 *>(dst + i) = oh;
-                        *reinterpret_cast<uint4 *>(d_lo + i) = ol;
-                        *reinterpret_cast<uint4 *>(d_h2 + i) = oh;
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (col0 + i < c.N) {
-                            const float a = acc[ch * 32 + i];
-                            const __half h = __float2half_rn(a);
-                            const __half l = __float2half_rn(a - __half2float(h));
-                            dst[i] = h;
-                            d_lo[i] = l;
-                            d_h2[i] = h;
-                        }
-                }
+            for (int i = 0; i < HN / 2; ++i) {
+                __half2 h = *reinterpret_cast<__half2 *>(&hi[i]);
+                float2 hf = __half22float2(h);
+                __half2 l = __floats2half2_rn(acc[2 * i] - hf.x, acc[2 * i + 1] - hf.y);
+                lo[i] = *reinterpret_cast<uint32_t *>(&l);
             }
+            store_plane<HN>(c, wstage, lo, p.out + p.plane_stride, p.ldo);
         }
     }
 };
@@ -392,32 +535,46 @@ struct GemmShape {
     int chunk_iters;
 };
 
-template <int BLOCK_N>
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;  // TMA warp + MMA warp + 8 epilogue warps
+constexpr int NUM_EPI_THREADS = NUM_EPI_WARPS * 32;
+__device__ __forceinline__ void epi_bar_sync() {  // named barrier 1: the epilogue threads only
+    asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory");
+}
+
+template <int BLOCK_N, int EPI_STAGE_BYTES>
 struct SmemLayout {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BLOCK_N <= 128) ? 6 : 4;
-    static constexpr int TAIL_BYTES = 4096;  // barriers, tmem slot, epilogue scratch
-    static constexpr int TOTAL = STAGES * STAGE_BYTES + TAIL_BYTES + 1024 /* alignment slack */;
-    static_assert((2 * STAGES + 4) * 8 + 16 + 2 * BLOCK_N * 4 <= TAIL_BYTES, "tail");
+    static constexpr int TAIL_BYTES = 8192;  // barriers, tmem slot, epilogue scratch
+    static constexpr int MAX_SMEM = 232448;  // 227 KB
+    static constexpr int STAGES_FIT = (MAX_SMEM - 1024 - TAIL_BYTES - EPI_STAGE_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + TAIL_BYTES + 1024;
+    static_assert(STAGES >= 3, "pipeline too shallow");
+    static_assert((2 * 6 + 4) * 8 + 16 + SCRATCH_FLOATS * 4 <= TAIL_BYTES, "tail");
 };
 
-template <int BLOCK_N, class Epi>
+// A_MN = false: A is (M, Kd) row-major (K-major), map_a box = 64 k x 128 rows.
+// A_MN = true : A is given TRANSPOSED, (Kd, M) row-major (MN-major operand), map_a
+//               box = 64 m x 64 k-rows, two boxes per stage.  This is how dtext = G^T . V
+//               reads G without anybody materialising G^T.
+template <int BLOCK_N, class Epi, bool A_MN = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const GemmShape shape, const typename Epi::Params ep) {
-    using L = SmemLayout<BLOCK_N>;
+    using L = SmemLayout<BLOCK_N, Epi::STAGE_BYTES>;
     constexpr int STAGES = L::STAGES;
+    constexpr int HN = BLOCK_N / 2;
     constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 32) ? 32 : (2 * BLOCK_N <= 64) ? 64
                                    : (2 * BLOCK_N <= 128) ? 128 : (2 * BLOCK_N <= 256) ? 256 : 512;
-    static_assert(2 * BLOCK_N <= 512, "two accumulators must fit in TMEM");
-    static_assert(BLOCK_N % 32 == 0 && BLOCK_N >= 32 && BLOCK_N <= 256, "BLOCK_N");
+    static_assert(BLOCK_N == 128, "epilogues are written for 128-wide tiles");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                 ~(uintptr_t)1023);
-    uint8_t *tail = smem + STAGES * L::STAGE_BYTES;
+    uint8_t *epi_stage = smem + STAGES * L::STAGE_BYTES;
+    uint8_t *tail = epi_stage + Epi::STAGE_BYTES;
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(tail);
     uint64_t *empty_bar = full_bar + STAGES;
     uint64_t *tfull_bar = empty_bar + STAGES;  // [2] accumulator ready
@@ -445,7 +602,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&tfull_bar[b], 1);
-            mbar_init(&tempty_bar[b], NUM_EPI_THREADS / 32);
+            mbar_init(&tempty_bar[b], NUM_EPI_WARPS);
         }
         fence_barrier_init();
     }
@@ -466,7 +623,13 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
                     uint8_t *sa = smem + stage * L::STAGE_BYTES;
-                    tma_load_2d(sa, &map_a, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M);
+                    if (A_MN) {
+                        tma_load_2d(sa, &map_a, &full_bar[stage], m_blk * BLOCK_M, kb * BLOCK_K);
+                        tma_load_2d(sa + L::A_BYTES / 2, &map_a, &full_bar[stage],
+                                    m_blk * BLOCK_M + 64, kb * BLOCK_K);
+                    } else {
+                        tma_load_2d(sa, &map_a, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M);
+                    }
                     tma_load_2d(sa + L::A_BYTES, &map_b, &full_bar[stage], kb * BLOCK_K,
                                 n_blk * BLOCK_N);
                     if (++stage == STAGES) {
@@ -479,7 +642,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BLOCK_N);
+            constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BLOCK_N, A_MN ? 1 : 0);
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0;  // accumulator-chunk counter: buffer = cc & 1
@@ -495,13 +658,23 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         mbar_wait(&full_bar[stage], phase);
                         tcgen05_fence_after();
                         const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-                        const uint64_t adesc = make_smem_desc(sa);
                         const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
+                        if (A_MN) {
+                            // slabs of 64 m are A_BYTES/2 apart; a UMMA_K step is 16 rows = 2048 B
+                            const uint64_t adesc = make_smem_desc_mn(sa, L::A_BYTES / 2);
 #pragma unroll
-                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                            // +32 bytes per UMMA_K step inside the swizzled 128-byte row
-                            umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
-                                     idesc, (uint32_t)((kb > kb0) || (k > 0)));
+                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                umma_f16(tmem_d, adesc + (uint64_t)(k * (UMMA_K * 128 / 16)),
+                                         bdesc + (uint64_t)(k * 2), idesc,
+                                         (uint32_t)((kb > kb0) || (k > 0)));
+                        } else {
+                            const uint64_t adesc = make_smem_desc(sa);
+#pragma unroll
+                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                                // +32 bytes per UMMA_K step inside the swizzled 128-byte row
+                                umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
+                                         idesc, (uint32_t)((kb > kb0) || (k > 0)));
+                            }
                         }
                         umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
                         if (++stage == STAGES) {
@@ -514,30 +687,36 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
         }
     } else {
-        // ===================== epilogue warps 2..5 =====================
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        // ===================== epilogue warps 2..9 =====================
         EpiCtx c;
+        c.q = warp & 3;               // TMEM lane quarter this warp may access
+        c.half = (warp - 2) >> 2;     // column half
+        c.warp_slot = warp - 2;
+        c.lane = lane;
         c.M = shape.M;
         c.N = shape.N;
-        c.tid = q * 32 + lane;
+        c.tid = c.q * 32 + lane;
+        c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
+        c.stage = epi_stage;
         uint32_t cc = 0;
         int lt = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
             c.m_blk = t % num_m;
             c.n_blk = t / num_m;
             c.m0 = c.m_blk * BLOCK_M;
-            c.n0 = c.n_blk * BLOCK_N;
+            c.n0 = c.n_blk * BLOCK_N + c.half * HN;
             c.par = lt & 1;
-            float acc[BLOCK_N];
+            float acc[HN];
             for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
                 const uint32_t buf = cc & 1;
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BLOCK_N;
+                const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * BLOCK_N +
+                                       (uint32_t)(c.half * HN);
                 mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
                 tcgen05_fence_after();
                 if (ck == 0) {
 #pragma unroll
-                    for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+                    for (int ch = 0; ch < HN / 32; ++ch) {
                         float v[32];
                         tmem_ld32(taddr + ch * 32, v);
 #pragma unroll
@@ -545,7 +724,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     }
                 } else {
 #pragma unroll
-                    for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+                    for (int ch = 0; ch < HN / 32; ++ch) {
                         float v[32];
                         tmem_ld32(taddr + ch * 32, v);
 #pragma unroll
@@ -556,7 +735,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
             }
-            Epi::template run<BLOCK_N>(ep, c, acc);
+            Epi::template run<HN>(ep, c, acc);
         }
     }
 

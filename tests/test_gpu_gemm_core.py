@@ -63,3 +63,38 @@ def test_gemm_identity_pattern_localises_descriptor_bugs():
     ref = a.float() @ b.float().t()
     bad = (c != ref).nonzero()
     assert bad.numel() == 0, f"first mismatches (m, n): {bad[:8].tolist()}"
+
+
+def _gemm_at(at, b, alpha=1.0):
+    """A passed transposed: at is (Kd, M).  Exercises the MN-major A descriptor."""
+    lib = milnce_b200._lib.load()
+    Kd, M = at.shape
+    N = b.shape[0]
+    c = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
+    rc = lib.b200head_gemm_at_f16(ctypes.c_void_p(at.data_ptr()), ctypes.c_void_p(b.data_ptr()),
+                                  ctypes.c_void_p(c.data_ptr()), M, N, Kd, at.stride(0), b.stride(0),
+                                  c.stride(0), ctypes.c_float(alpha), milnce_b200._lib.stream_ptr())
+    milnce_b200._lib.check(rc, "gemm_at_f16")
+    torch.cuda.synchronize()
+    return c
+
+
+@pytest.mark.parametrize("M,N,Kd", [
+    (128, 128, 64),
+    (128, 128, 256),
+    (256, 256, 1024),
+    (4096, 512, 2048),   # the dtext GEMM shape class (M = B*K, N = D, K = B)
+    (200, 72, 136),      # ragged everywhere
+])
+def test_gemm_mn_major_a_matches_torch(M, N, Kd):
+    g = torch.Generator(device="cuda").manual_seed(M + N * 5 + Kd * 11)
+    ldat = (M + 7) // 8 * 8
+    ldb = (Kd + 7) // 8 * 8
+    at = torch.randn(Kd, ldat, generator=g, device="cuda").half()[:, :M]
+    b = torch.randn(N, ldb, generator=g, device="cuda").half()[:, :Kd]
+    c = _gemm_at(at, b, alpha=2.0)
+    ref = 2.0 * (at.float().t() @ b.float().t())
+    assert not torch.isnan(c).any()
+    err = rel_err(c.cpu().numpy(), ref.cpu().numpy())
+    print(f"gemm_at {M}x{N}x{Kd}: rel err {err:.3e}")
+    assert err < 2e-6
