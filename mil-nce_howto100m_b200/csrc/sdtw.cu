@@ -21,6 +21,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "sdtw_fused.cuh"
 
 namespace {
 
@@ -438,6 +439,24 @@ extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M,
     float *Dm = reinterpret_cast<float *>(ax + a.off_d);
     float *nx = reinterpret_cast<float *>(ax + a.off_nx);
     float *ny = reinterpret_cast<float *>(ax + a.off_ny);
+    if (fused::eligible(N, M, d, dist_kind)) {
+        // short sequences: one fused kernel per pair (tensor-core distance tile + wavefront)
+        float4 *cellp = reinterpret_cast<float4 *>(ax + a.off_cell);
+        const int smem = (int)sizeof(fused::FwdSmem);
+        if (dist_kind == B200HEAD_DIST_COSINE) {
+            B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<0>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            fused::fwd_kernel<0><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
+                                                       nx, ny);
+        } else {
+            B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<1>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            fused::fwd_kernel<1><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
+                                                       nx, ny);
+        }
+        B200_LAUNCH_OK("sdtw fused forward kernel");
+        return 0;
+    }
     dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
     if (dist_kind == B200HEAD_DIST_COSINE)
         dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
@@ -478,6 +497,22 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     float *ny = reinterpret_cast<float *>(ax + a.off_ny);
     float *rsum = reinterpret_cast<float *>(ax + a.off_rsum);
     float *csum = reinterpret_cast<float *>(ax + a.off_csum);
+    if (fused::eligible(N, M, d, dist_kind)) {
+        const int smem = (int)sizeof(fused::BwdSmem);
+        if (dist_kind == B200HEAD_DIST_COSINE) {
+            B200_CUDA_OK(cudaFuncSetAttribute(fused::bwd_kernel<0>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            fused::bwd_kernel<0><<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E,
+                                                       dx, dy);
+        } else {
+            B200_CUDA_OK(cudaFuncSetAttribute(fused::bwd_kernel<1>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            fused::bwd_kernel<1><<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E,
+                                                       dx, dy);
+        }
+        B200_LAUNCH_OK("sdtw fused backward kernel");
+        return 0;
+    }
     const int T = std::max(32, (N + 31) / 32 * 32);
     const size_t sh = 2 * (size_t)(T + 1) * sizeof(float2) + (size_t)M * sizeof(float);
     dim3 gx((d + GD - 1) / GD, (N + GR - 1) / GR, B), gy((d + GD - 1) / GD, (M + GR - 1) / GR, B);
@@ -599,3 +634,9 @@ extern "C" int sdtw_forward_noalloc(const float *x, const float *y, int B, int N
     B200_LAUNCH_OK("sdtw_forward_noalloc dp_fwd_kernel");
     return 0;
 }
+
+#ifdef SDTW_PROFILE
+extern "C" int sdtw_debug_read(long long *host16) {
+    return (int)cudaMemcpyFromSymbol(host16, fused::g_prof, sizeof(long long) * 16);
+}
+#endif

@@ -46,7 +46,13 @@ def _compare(x, y, gamma, bw, dist, grad_out=None, tol=1e-5, name=""):
     e_dy = rel_err(dy.cpu().numpy(), dyr)
     print(f"{name} {dist} g={gamma} bw={bw}: R {e_R:.2e} out {e_out:.2e} E {e_E:.2e} "
           f"dX {e_dx:.2e} dY {e_dy:.2e}")
-    assert max(e_R, e_out, e_E, e_dx, e_dy) < tol, name
+    assert max(e_R, e_out) < tol, name
+    # E and the input gradients see D through exp(./gamma): merely rounding D to float32 (which
+    # the reference does too, its distance function runs in float32) perturbs E by about
+    # ulp(|D|)/gamma.  For cosine |D| < e^2 and that stays below 1e-5; for the unnormalised
+    # distances it does not, so the bound scales with |D|max there.
+    gtol = max(tol, 8 * 2.0 ** -24 * float(np.max(np.abs(D))) / g32)
+    assert max(e_E, e_dx, e_dy) < gtol, (name, gtol)
 
 
 @pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "sdtw_*.npz"))),
