@@ -541,9 +541,9 @@ __device__ __forceinline__ void epi_bar_sync() {  // named barrier 1: the epilog
     asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory");
 }
 
-template <int BLOCK_N, int EPI_STAGE_BYTES>
+template <int BLOCK_N, int EPI_STAGE_BYTES, int MB>
 struct SmemLayout {
-    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+    static constexpr int A_BYTES = MB * BLOCK_M * BLOCK_K * 2;  // MB row blocks of 128
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TAIL_BYTES = 8192;  // barriers, tmem slot, epilogue scratch
@@ -557,18 +557,28 @@ struct SmemLayout {
 
 // A_MN = false: A is (M, Kd) row-major (K-major), map_a box = 64 k x 128 rows.
 // A_MN = true : A is given TRANSPOSED, (Kd, M) row-major (MN-major operand), map_a
-//               box = 64 m x 64 k-rows, two boxes per stage.  This is how dtext = G^T . V
+//               box = 64 m x 64 k-rows, two boxes per 128 rows.  This is how dtext = G^T . V
 //               reads G without anybody materialising G^T.
-template <int BLOCK_N, class Epi, bool A_MN = false>
+// MB          : row blocks of 128 per tile.  These GEMMs run at the L2 -> SM bandwidth limit
+//               (measured 12.3 TB/s = the chip-wide L2 cap with 128x128 tiles at 41 % tensor-pipe
+//               activity), so a 256x128 tile - two accumulators sharing one B tile - moves 25 %
+//               fewer operand bytes per FLOP.  MB = 2 needs the whole K loop in one chunk.
+// N_FAST      : tile order.  false: m fastest (CTAs in flight share B tiles);  true: n fastest
+//               (CTAs in flight share the A rows - for skinny N this keeps a huge A from being
+//               streamed from HBM once per n-block).
+template <int BLOCK_N, class Epi, bool A_MN = false, int MB = 1, bool N_FAST = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const GemmShape shape, const typename Epi::Params ep) {
-    using L = SmemLayout<BLOCK_N, Epi::STAGE_BYTES>;
+    using L = SmemLayout<BLOCK_N, Epi::STAGE_BYTES, MB>;
     constexpr int STAGES = L::STAGES;
     constexpr int HN = BLOCK_N / 2;
-    constexpr uint32_t TMEM_COLS = (2 * BLOCK_N <= 32) ? 32 : (2 * BLOCK_N <= 64) ? 64
-                                   : (2 * BLOCK_N <= 128) ? 128 : (2 * BLOCK_N <= 256) ? 256 : 512;
+    constexpr int TILE_M = MB * BLOCK_M;
+    constexpr int ACC_COLS = MB * BLOCK_N;  // TMEM columns per accumulator buffer
+    constexpr uint32_t TMEM_COLS = (2 * ACC_COLS <= 256) ? 256 : 512;
     static_assert(BLOCK_N == 128, "epilogues are written for 128-wide tiles");
+    static_assert(MB == 1 || MB == 2, "one or two row blocks");
+    static_assert(2 * ACC_COLS <= 512, "two accumulator buffers must fit in TMEM");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -585,12 +595,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    const int num_m = (shape.M + BLOCK_M - 1) / BLOCK_M;
+    const int num_m = (shape.M + TILE_M - 1) / TILE_M;
     const int num_n = (shape.N + BLOCK_N - 1) / BLOCK_N;
     const int num_tiles = num_m * num_n;
     const int k_iters = (shape.Kd + BLOCK_K - 1) / BLOCK_K;
-    const int chunk_iters = (shape.chunk_iters > 0 && shape.chunk_iters < k_iters) ? shape.chunk_iters
-                                                                                   : k_iters;
+    const int chunk_iters = (MB == 1 && shape.chunk_iters > 0 && shape.chunk_iters < k_iters)
+                                ? shape.chunk_iters : k_iters;
     const int n_chunks = (k_iters + chunk_iters - 1) / chunk_iters;
 
     if (warp == 0 && lane == 0) {
@@ -618,17 +628,22 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m_blk = t % num_m, n_blk = t / num_m;
+                const int m_blk = N_FAST ? t / num_n : t % num_m;
+                const int n_blk = N_FAST ? t % num_n : t / num_m;
                 for (int kb = 0; kb < k_iters; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
                     uint8_t *sa = smem + stage * L::STAGE_BYTES;
                     if (A_MN) {
-                        tma_load_2d(sa, &map_a, &full_bar[stage], m_blk * BLOCK_M, kb * BLOCK_K);
-                        tma_load_2d(sa + L::A_BYTES / 2, &map_a, &full_bar[stage],
-                                    m_blk * BLOCK_M + 64, kb * BLOCK_K);
+#pragma unroll
+                        for (int sl = 0; sl < 2 * MB; ++sl)  // 64-wide slabs of the M index
+                            tma_load_2d(sa + sl * (BLOCK_K * 128), &map_a, &full_bar[stage],
+                                        m_blk * TILE_M + sl * 64, kb * BLOCK_K);
                     } else {
-                        tma_load_2d(sa, &map_a, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M);
+#pragma unroll
+                        for (int rb = 0; rb < MB; ++rb)
+                            tma_load_2d(sa + rb * (BLOCK_M * BLOCK_K * 2), &map_a, &full_bar[stage],
+                                        kb * BLOCK_K, m_blk * TILE_M + rb * BLOCK_M);
                     }
                     tma_load_2d(sa + L::A_BYTES, &map_b, &full_bar[stage], kb * BLOCK_K,
                                 n_blk * BLOCK_N);
@@ -651,7 +666,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     const uint32_t buf = cc & 1;
                     mbar_wait(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
                     tcgen05_fence_after();
-                    const uint32_t tmem_d = tmem_base + buf * BLOCK_N;
+                    const uint32_t tmem_d = tmem_base + buf * ACC_COLS;
                     const int kb0 = ck * chunk_iters;
                     const int kb1 = min(k_iters, kb0 + chunk_iters);
                     for (int kb = kb0; kb < kb1; ++kb) {
@@ -659,21 +674,26 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         tcgen05_fence_after();
                         const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
                         const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
-                        if (A_MN) {
-                            // slabs of 64 m are A_BYTES/2 apart; a UMMA_K step is 16 rows = 2048 B
-                            const uint64_t adesc = make_smem_desc_mn(sa, L::A_BYTES / 2);
 #pragma unroll
-                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                                umma_f16(tmem_d, adesc + (uint64_t)(k * (UMMA_K * 128 / 16)),
-                                         bdesc + (uint64_t)(k * 2), idesc,
-                                         (uint32_t)((kb > kb0) || (k > 0)));
-                        } else {
-                            const uint64_t adesc = make_smem_desc(sa);
+                        for (int rb = 0; rb < MB; ++rb) {
+                            const uint32_t sarb = sa + rb * (BLOCK_M * BLOCK_K * 2);
+                            const uint32_t td = tmem_d + rb * BLOCK_N;
+                            if (A_MN) {
+                                // slabs of 64 m are 8 KB apart; a UMMA_K step is 16 rows = 2048 B
+                                const uint64_t adesc = make_smem_desc_mn(sarb, BLOCK_K * 128);
 #pragma unroll
-                            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                                // +32 bytes per UMMA_K step inside the swizzled 128-byte row
-                                umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
-                                         idesc, (uint32_t)((kb > kb0) || (k > 0)));
+                                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                                    umma_f16(td, adesc + (uint64_t)(k * (UMMA_K * 128 / 16)),
+                                             bdesc + (uint64_t)(k * 2), idesc,
+                                             (uint32_t)((kb > kb0) || (k > 0)));
+                            } else {
+                                const uint64_t adesc = make_smem_desc(sarb);
+#pragma unroll
+                                for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                                    // +32 bytes per UMMA_K step inside the swizzled 128-byte row
+                                    umma_f16(td, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
+                                             idesc, (uint32_t)((kb > kb0) || (k > 0)));
+                                }
                             }
                         }
                         umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
@@ -700,21 +720,59 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         c.scratch = epi_scratch;
         c.stage = epi_stage;
         uint32_t cc = 0;
-        int lt = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
-            c.m_blk = t % num_m;
-            c.n_blk = t / num_m;
-            c.m0 = c.m_blk * BLOCK_M;
+        int runs = 0;  // epilogue invocations so far (parity of the smem scratch buffers)
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const int m_blk = N_FAST ? t / num_n : t % num_m;
+            c.n_blk = N_FAST ? t % num_n : t / num_m;
             c.n0 = c.n_blk * BLOCK_N + c.half * HN;
-            c.par = lt & 1;
-            float acc[HN];
-            for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
+            if (MB == 1) {
+                c.m_blk = m_blk;
+                c.m0 = m_blk * BLOCK_M;
+                c.par = runs & 1;
+                ++runs;
+                float acc[HN];
+                for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
+                    const uint32_t buf = cc & 1;
+                    const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * ACC_COLS +
+                                           (uint32_t)(c.half * HN);
+                    mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
+                    tcgen05_fence_after();
+                    if (ck == 0) {
+#pragma unroll
+                        for (int ch = 0; ch < HN / 32; ++ch) {
+                            float v[32];
+                            tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) acc[ch * 32 + i] = v[i];
+                        }
+                    } else {
+#pragma unroll
+                        for (int ch = 0; ch < HN / 32; ++ch) {
+                            float v[32];
+                            tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) acc[ch * 32 + i] += v[i];
+                        }
+                    }
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
+                }
+                Epi::template run<HN>(ep, c, acc);
+            } else {
+                // two row blocks, one chunk: drain and process them one after the other
                 const uint32_t buf = cc & 1;
-                const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * BLOCK_N +
-                                       (uint32_t)(c.half * HN);
                 mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
                 tcgen05_fence_after();
-                if (ck == 0) {
+#pragma unroll 1
+                for (int rb = 0; rb < MB; ++rb) {
+                    c.m_blk = m_blk * MB + rb;
+                    c.m0 = c.m_blk * BLOCK_M;
+                    c.par = runs & 1;
+                    ++runs;
+                    const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * ACC_COLS +
+                                           (uint32_t)(rb * BLOCK_N + c.half * HN);
+                    float acc[HN];
 #pragma unroll
                     for (int ch = 0; ch < HN / 32; ++ch) {
                         float v[32];
@@ -722,20 +780,15 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                         for (int i = 0; i < 32; ++i) acc[ch * 32 + i] = v[i];
                     }
-                } else {
-#pragma unroll
-                    for (int ch = 0; ch < HN / 32; ++ch) {
-                        float v[32];
-                        tmem_ld32(taddr + ch * 32, v);
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) acc[ch * 32 + i] += v[i];
+                    if (rb == MB - 1) {
+                        tcgen05_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // both row blocks drained
                     }
+                    Epi::template run<HN>(ep, c, acc);
                 }
-                tcgen05_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
+                ++cc;
             }
-            Epi::template run<HN>(ep, c, acc);
         }
     }
 
