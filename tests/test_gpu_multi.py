@@ -1,0 +1,68 @@
+"""Two-GPU NCCL check of GatheredMILNCELoss (skipped with fewer than two devices).
+
+Each rank holds its shard of the global batch; the sharded module must return the same
+loss on every rank and the local gradient slices of the single-GPU MILNCELoss evaluated
+on the gathered tensors (what reference utils.py:20-24 hands back)."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import milnce_b200
+        B, K, D = 1024, 4, 512
+        b = B // world
+        g = torch.Generator().manual_seed(77)
+        V = (torch.randn(B, D, generator=g) * 0.1).bfloat16().cuda()
+        T = (torch.randn(B * K, D, generator=g) * 0.1).bfloat16().cuda()
+        v_loc = V[rank * b:(rank + 1) * b].clone().requires_grad_(True)
+        t_loc = T[rank * b * K:(rank + 1) * b * K].clone().requires_grad_(True)
+        loss = milnce_b200.GatheredMILNCELoss()(v_loc, t_loc)
+        loss.backward()
+        Vf = V.clone().requires_grad_(True)
+        Tf = T.clone().requires_grad_(True)
+        ref = milnce_b200.MILNCELoss()(Vf, Tf)
+        ref.backward()
+        torch.cuda.synchronize()
+        ok = abs(loss.item() - ref.item()) < 1e-5 * abs(ref.item())
+        dv_ref = Vf.grad[rank * b:(rank + 1) * b].float()
+        dt_ref = Tf.grad[rank * b * K:(rank + 1) * b * K].float()
+        e1 = ((v_loc.grad.float() - dv_ref).norm() / dv_ref.norm()).item()
+        e2 = ((t_loc.grad.float() - dt_ref).norm() / dt_ref.norm()).item()
+        ok = ok and e1 < 5e-3 and e2 < 5e-3   # both sides are rounded to bf16 by the module API
+        out[rank] = 1 if ok else 0
+        if not ok:
+            print(f"rank {rank}: loss {loss.item()} vs {ref.item()} dV {e1} dT {e2}", flush=True)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_gathered_loss_two_gpus_nccl():
+    world = 2
+    out = mp.get_context("spawn").Array("i", [0] * world)
+    mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert list(out) == [1] * world
