@@ -17,6 +17,7 @@
 //   pass C  recompute S^T tile -> G^T (n*K, B)
 //   dvideo = G . T, dtext = G^T . V  (two more tcgen05 GEMMs, fp32 out)
 #include <algorithm>
+#include <type_traits>
 
 #include <cuda_bf16.h>
 
@@ -103,10 +104,23 @@ template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16
 template <typename T>
 __global__ void absmax_kernel(const T *__restrict__ x, size_t count, unsigned int *out_bits) {
     float m = 0.f;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count;
+    constexpr int VEC = 16 / sizeof(T);  // elements per 16-byte load
+    const size_t nvec = (((uintptr_t)x & 15) == 0) ? count / VEC : 0;
+    const uint4 *xv = reinterpret_cast<const uint4 *>(x);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec;
          i += (size_t)gridDim.x * blockDim.x) {
-        float v = fabsf(to_f32(x[i]));
-        if (v == v && v <= 3.0e38f) m = fmaxf(m, v);  // ignore NaN/inf for the scale choice
+        const uint4 q = xv[i];
+        const T *e = reinterpret_cast<const T *>(&q);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const float v = fabsf(to_f32(e[j]));
+            if (v == v && v <= 3.0e38f) m = fmaxf(m, v);  // ignore NaN/inf for the scale choice
+        }
+    }
+    for (size_t i = nvec * VEC + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const float v = fabsf(to_f32(x[i]));
+        if (v == v && v <= 3.0e38f) m = fmaxf(m, v);
     }
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out_bits, __float_as_uint(m));
@@ -204,6 +218,54 @@ __global__ void stage_operand_kernel(const T *__restrict__ in, int rows, int D,
     }
 }
 
+// bf16 fast path of the above (planes == 1, D % 8 == 0, 16-byte aligned rows): 64 x 64 tiles,
+// 16-byte global loads and stores on both the K-major copy and the transposed copy.
+__global__ void __launch_bounds__(256)
+stage_bf16_kernel(const __nv_bfloat16 *__restrict__ in, int rows, int D,
+                  const float *__restrict__ scale_ptr, __half *__restrict__ outk, long long ldk,
+                  __half *__restrict__ outt, long long ldt) {
+    __shared__ __half tile[64][64 + 2];  // +2 halves: conflict-free column reads
+    const float sc = *scale_ptr;
+    const int r0 = blockIdx.y * 64, d0 = blockIdx.x * 64;
+    const int tid = threadIdx.x;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int g = tid + h * 256;          // 512 granules of 8 elements
+        const int rr = g >> 3, dc = (g & 7) * 8;
+        const int r = r0 + rr, d = d0 + dc;
+        __align__(16) __half hv[8];
+        if (r < rows && d < D) {              // D % 8 == 0: a granule is all in or all out
+            const uint4 q = *reinterpret_cast<const uint4 *>(in + (size_t)r * D + d);
+            const __nv_bfloat16 *e = reinterpret_cast<const __nv_bfloat16 *>(&q);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(__bfloat162float(e[j]) * sc);
+            *reinterpret_cast<uint4 *>(outk + (size_t)r * ldk + d) = *reinterpret_cast<uint4 *>(hv);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) tile[rr][dc + j] = hv[j];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int g = tid + h * 256;
+        const int dd = g >> 3, rc = (g & 7) * 8;   // transposed granule: feature dd, 8 rows from rc
+        const int d = d0 + dd, r = r0 + rc;
+        if (d >= D || r >= rows) continue;
+        __align__(16) __half hv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) hv[j] = tile[rc + j][dd];
+        __half *dst = outt + (size_t)d * ldt + r;
+        if (r + 8 <= rows && ((((uintptr_t)dst) & 15) == 0)) {
+            *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<uint4 *>(hv);
+        } else {
+            for (int j = 0; j < 8 && r + j < rows; ++j) dst[j] = hv[j];
+        }
+    }
+}
+
 // ----------------------------------------------------------------------------
 // finalize: one warp per owned sample
 // ----------------------------------------------------------------------------
@@ -217,13 +279,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // merge the per-tile partial log-sum-exps of 32 samples per block: lane = sample (coalesced
-// reads), the block's 8 warps stride over the partials, then combine through smem.
+// reads), the block's 32 warps stride over the partials, then combine through smem.
 //   part_r[t][w], t < nb_r          -> row_i = lse over all text columns
 //   part_c[t][w*K + k], t < nb_c    -> col_i = lse over all video rows and the K candidates
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict__ part_c, int K, int n,
                       int nb_r, int nb_c, float *__restrict__ rowcol) {
-    __shared__ float sm[8][32], ss[8][32];
+    constexpr int NW = 32;
+    __shared__ float sm[NW][32], ss[NW][32];
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     const int w = blockIdx.x * 32 + lane;
     float m = -INFINITY, s = 0.f;
@@ -236,9 +299,9 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
         }
     };
     if (w < n) {
-        for (int t = wp; t < nb_r; t += 8) push(part_r[(size_t)t * n + w]);
+        for (int t = wp; t < nb_r; t += NW) push(part_r[(size_t)t * n + w]);
         const size_t nk = (size_t)n * K;
-        for (int t = wp; t < nb_c; t += 8)
+        for (int t = wp; t < nb_c; t += NW)
             for (int k = 0; k < K; ++k) push(part_c[(size_t)t * nk + (size_t)w * K + k]);
     }
     sm[wp][lane] = m;
@@ -246,9 +309,9 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     __syncthreads();
     if (wp == 0 && w < n) {
         float mm = sm[0][lane];
-        for (int j = 1; j < 8; ++j) mm = fmaxf(mm, sm[j][lane]);
+        for (int j = 1; j < NW; ++j) mm = fmaxf(mm, sm[j][lane]);
         float tot = 0.f;
-        for (int j = 0; j < 8; ++j)
+        for (int j = 0; j < NW; ++j)
             if (sm[j][lane] > -INFINITY) tot += ss[j][lane] * __expf(sm[j][lane] - mm);
         rowcol[w] = mm + logf(tot);  // = logaddexp(row_i, col_i) = den_i  (loss.py:16-17)
     }
@@ -350,14 +413,26 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
     absmax_kernel<T><<<(unsigned)std::min<size_t>((ct + 1023) / 1024, 1184), 256, 0, st>>>(
         text, ct, &sc->absmax_bits[1]);
     scalars_forward_kernel<<<1, 1, 0, st>>>(sc);
-    dim3 blk(32, 8);
-    dim3 gv((p.D + 31) / 32, (p.B + 31) / 32), gt((p.D + 31) / 32, (unsigned)((p.BK + 31) / 32));
-    stage_operand_kernel<T><<<gv, blk, 0, st>>>(video, p.B, p.D, &sc->s_video, p.P, true,
-                                                reinterpret_cast<__half *>(ws + p.off_vk), p.ld_vk,
-                                                reinterpret_cast<__half *>(ws + p.off_vt), p.ld_vt);
-    stage_operand_kernel<T><<<gt, blk, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, p.P, false,
-                                                reinterpret_cast<__half *>(ws + p.off_tk), p.ld_tk,
-                                                reinterpret_cast<__half *>(ws + p.off_tt), p.ld_tt);
+    __half *vk_ = reinterpret_cast<__half *>(ws + p.off_vk), *vt_ = reinterpret_cast<__half *>(ws + p.off_vt);
+    __half *tk_ = reinterpret_cast<__half *>(ws + p.off_tk), *tt_ = reinterpret_cast<__half *>(ws + p.off_tt);
+    bool fast = false;
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+        fast = (p.D % 8 == 0) && (((uintptr_t)video & 15) == 0) && (((uintptr_t)text & 15) == 0);
+        if (fast) {
+            dim3 gv((p.D + 63) / 64, (p.B + 63) / 64), gt((p.D + 63) / 64, (unsigned)((p.BK + 63) / 64));
+            stage_bf16_kernel<<<gv, 256, 0, st>>>(video, p.B, p.D, &sc->s_video, vk_, p.ld_vk, vt_, p.ld_vt);
+            stage_bf16_kernel<<<gt, 256, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, tk_, p.ld_tk, tt_,
+                                                  p.ld_tt);
+        }
+    }
+    if (!fast) {
+        dim3 blk(32, 8);
+        dim3 gv((p.D + 31) / 32, (p.B + 31) / 32), gt((p.D + 31) / 32, (unsigned)((p.BK + 31) / 32));
+        stage_operand_kernel<T><<<gv, blk, 0, st>>>(video, p.B, p.D, &sc->s_video, p.P, true, vk_, p.ld_vk,
+                                                    vt_, p.ld_vt);
+        stage_operand_kernel<T><<<gt, blk, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, p.P, false, tk_,
+                                                    p.ld_tk, tt_, p.ld_tt);
+    }
     B200_LAUNCH_OK("staging kernels");
     return 0;
 }
@@ -418,7 +493,7 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
                                                      p.chunk_s, ec, st, "milnce forward column block");
         if (rc) return rc;
     }
-    merge_partials_kernel<<<(p.n + 31) / 32, 256, 0, st>>>(pr, pc, p.K, p.n, p.nb_r, p.nb_c, rowcol);
+    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, pc, p.K, p.n, p.nb_r, p.nb_c, rowcol);
     const int warps_per_block = 8;
     finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
         video, text, rowcol, p.K, p.D, p.i0, p.n, den, nom, diff);
