@@ -83,6 +83,8 @@ def _declare(lib):
     lib.b200head_gemm_tn_f16.argtypes = [vp, vp, fp, i32, i32, i32, i32, i32, i32, f32, vp]
     lib.b200head_gemm_at_f16.restype = i32
     lib.b200head_gemm_at_f16.argtypes = [vp, vp, fp, i32, i32, i32, i32, i32, i32, f32, vp]
+    lib.b200head_gemm2_f16.restype = i32
+    lib.b200head_gemm2_f16.argtypes = [vp, vp, fp, i32, i32, i32, i32, i32, i32, f32, i32, vp]
 
 
 def load():

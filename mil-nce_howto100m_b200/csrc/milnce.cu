@@ -17,12 +17,15 @@
 //   pass C  recompute S^T tile -> G^T (n*K, B)
 //   dvideo = G . T, dtext = G^T . V  (two more tcgen05 GEMMs, fp32 out)
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <type_traits>
 
 #include <cuda_bf16.h>
 
 #include "common.cuh"
 #include "tc_gemm.cuh"
+#include "tc_gemm2.cuh"
 
 namespace {
 
@@ -70,7 +73,8 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.ld_tt = (long long)align_up((size_t)p.P * p.BK, 8);
     p.ld_g = p.ld_tt;
     p.ld_gt = p.ld_vt;
-    p.nb_r = 2 * (int)((p.BK + BLOCK_N - 1) / BLOCK_N);  // one row partial per 64-column half tile
+    // one row partial per 64-column half tile; bf16 mode runs 256-wide pair tiles (all four written)
+    p.nb_r = (p.P == 1) ? 4 * (int)((p.BK + 255) / 256) : 2 * (int)((p.BK + BLOCK_N - 1) / BLOCK_N);
     // one column partial per 128-row block; bf16 mode runs 256-row tiles (both halves are written)
     p.nb_c = (p.P == 1) ? 2 * ((B + 255) / 256) : (B + 127) / 128;
     size_t o = 0;
@@ -403,6 +407,39 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     return 0;
 }
 
+// bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.  B200HEAD_GEMM=1cta in the
+// environment selects the one-CTA 256 x 128 kernel instead (for A/B measurements).
+bool use_2cta() {
+    static const bool v = [] {
+        const char *e = getenv("B200HEAD_GEMM");
+        return !(e && strcmp(e, "1cta") == 0);
+    }();
+    return v;
+}
+
+template <class Epi, bool A_MN = false, bool N_FAST = false>
+int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
+                 const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
+    if (!use_2cta()) return launch_gemm<Epi, A_MN, 2, N_FAST>(A, lda, Bm, ldb, M, N, Kd, 0, ep, stream, what);
+    using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
+    CUtensorMap ma, mb;
+    int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
+                  : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
+                                           tc::BLOCK_M);
+    if (rc) return rc;
+    rc = b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, tc::PAIR_N / 2);
+    if (rc) return rc;
+    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
+    const int max_pairs = num_sms() / 2;
+    const int pairs = tiles < max_pairs ? tiles : max_pairs;
+    tc::GemmShape shape{M, N, Kd, 0};
+    kern<<<2 * pairs, tc::NUM_THREADS, L::TOTAL, stream>>>(ma, mb, shape, ep);
+    B200_LAUNCH_OK(what);
+    return 0;
+}
+
 template <typename T>
 int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cudaStream_t st) {
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
@@ -470,8 +507,7 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         // one pass over S: row statistic per thread, column statistic by a cross-lane reduction
         tc::EpiRowCol::Params e{pr, (long long)p.n, pc, (long long)p.BK, &sc->inv_ss};
         const char *what = "milnce forward (fused row+column statistics)";
-        rc = (p.P == 1) ? launch_gemm<tc::EpiRowCol, false, 2>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK,
-                                                               Kd, p.chunk_s, e, st, what)
+        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd, e, st, what)
                         : launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd,
                                                      p.chunk_s, e, st, what);
         if (rc) return rc;
@@ -479,16 +515,16 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         // sharded: rows [i0, i0+n) x all columns -> row statistic of the owned samples
         tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, &sc->inv_ss};
         const __half *va = vk + (size_t)p.i0 * p.ld_vk;
-        rc = (p.P == 1) ? launch_gemm<tc::EpiRowCol, false, 2>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
-                                                               p.chunk_s, er, st, "milnce forward row block")
+        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, er, st,
+                                                     "milnce forward row block")
                         : launch_gemm<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
                                                      p.chunk_s, er, st, "milnce forward row block");
         if (rc) return rc;
         // all rows x columns of the owned samples -> their column statistic
         tc::EpiRowCol::Params ec{nullptr, 0, pc, (long long)p.n * p.K, &sc->inv_ss};
         const __half *tb = tk + (size_t)p.i0 * p.K * p.ld_tk;
-        rc = (p.P == 1) ? launch_gemm<tc::EpiRowCol, false, 2>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd,
-                                                               p.chunk_s, ec, st, "milnce forward column block")
+        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd, ec, st,
+                                                     "milnce forward column block")
                         : launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd,
                                                      p.chunk_s, ec, st, "milnce forward column block");
         if (rc) return rc;
@@ -524,8 +560,8 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     // row block: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, 0, p.K, &sc->inv_ss, fast};
     const __half *va = vk + (size_t)p.i0 * p.ld_vk;
-    rc = (p.P == 1) ? launch_gemm<tc::EpiG, false, 2>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s,
-                                                      gr, st, "milnce backward row block")
+    rc = (p.P == 1) ? launch_gemm2<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, gr, st,
+                                           "milnce backward row block")
                     : launch_gemm<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, gr, st,
                                             "milnce backward row block");
     if (rc) return rc;
@@ -533,8 +569,8 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
-    rc = (p.P == 1) ? launch_gemm<tc::EpiStore, false, 2, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK,
-                                                                p.chunk_g, sv, st, "milnce dvideo GEMM")
+    rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+                                                            "milnce dvideo GEMM")
                     : launch_gemm<tc::EpiStore, false, 1, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D,
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
@@ -549,15 +585,14 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
             // column block: G2 (B, n*K): row <-> sample r, column c <-> sample (i0*K + c) / K
             tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, 1, p.i0 * p.K, p.K,
                                 &sc->inv_ss, fast};
-            rc = launch_gemm<tc::EpiG, false, 2>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk,
-                                                 p.B, p.n * p.K, Kd, p.chunk_s, gc, st,
-                                                 "milnce backward column block");
+            rc = launch_gemm2<tc::EpiG>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
+                                        p.n * p.K, Kd, gc, st, "milnce backward column block");
             if (rc) return rc;
             g2 = gt;
             ld_g2 = p.ld_g2;
         }
-        rc = launch_gemm<tc::EpiStore, true, 2, true>(g2, ld_g2, vt, p.ld_vt, p.n * p.K, p.D, p.B,
-                                                      p.chunk_g, sd, st, "milnce dtext GEMM (MN-major G)");
+        rc = launch_gemm2<tc::EpiStore, true, true>(g2, ld_g2, vt, p.ld_vt, p.n * p.K, p.D, p.B, sd, st,
+                                                    "milnce dtext GEMM (MN-major G)");
         return rc;
     }
     // fp32 inputs (hi/lo planes): the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
@@ -657,4 +692,19 @@ extern "C" int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, in
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
     return launch_gemm<tc::EpiStore, true>(At, ldat, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                            "gemm_at_f16 test hook");
+}
+
+extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd, int lda,
+                                  int ldb, int ldc, float alpha, int a_transposed, void *stream) {
+    if (!A || !Bm || !C || M <= 0 || N <= 0 || Kd <= 0) {
+        b200::set_error("b200head_gemm2_f16: bad argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    return a_transposed ? launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep,
+                                                                 (cudaStream_t)stream, "gemm2 test hook")
+                        : launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep,
+                                                                   (cudaStream_t)stream, "gemm2 test hook");
 }

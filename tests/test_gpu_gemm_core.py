@@ -98,3 +98,38 @@ def test_gemm_mn_major_a_matches_torch(M, N, Kd):
     err = rel_err(c.cpu().numpy(), ref.cpu().numpy())
     print(f"gemm_at {M}x{N}x{Kd}: rel err {err:.3e}")
     assert err < 2e-6
+
+
+@pytest.mark.parametrize("transposed", [0, 1])
+@pytest.mark.parametrize("M,N,Kd", [
+    (256, 256, 64),      # one pair tile, one k-block
+    (256, 256, 512),
+    (1024, 512, 2048),   # several tiles per pair: TMEM double buffering across tiles
+    (8192, 512, 256),    # more tiles than CTA pairs
+    (300, 200, 136),     # ragged: the follower CTA's rows / columns partly or fully out of range
+    (100, 72, 72),
+])
+def test_gemm_cta_pair_kernel_matches_torch(M, N, Kd, transposed):
+    """tcgen05.mma.cta_group::2 path: 2-CTA clusters, peer-signalled TMA, multicast commits."""
+    lib = milnce_b200._lib.load()
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N * 7 + Kd + transposed)
+    ldk = (Kd + 7) // 8 * 8
+    b = torch.randn(N, ldk, generator=g, device="cuda").half()[:, :Kd]
+    if transposed:
+        ldm = (M + 7) // 8 * 8
+        a = torch.randn(Kd, ldm, generator=g, device="cuda").half()[:, :M]
+        ref = a.float().t() @ b.float().t()
+    else:
+        a = torch.randn(M, ldk, generator=g, device="cuda").half()[:, :Kd]
+        ref = a.float() @ b.float().t()
+    c = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
+    rc = lib.b200head_gemm2_f16(ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(b.data_ptr()),
+                                ctypes.c_void_p(c.data_ptr()), M, N, Kd, a.stride(0), b.stride(0),
+                                c.stride(0), ctypes.c_float(1.0), transposed,
+                                milnce_b200._lib.stream_ptr())
+    milnce_b200._lib.check(rc, "gemm2_f16")
+    torch.cuda.synchronize()
+    assert not torch.isnan(c).any()
+    err = rel_err(c.cpu().numpy(), ref.cpu().numpy())
+    print(f"gemm2 {M}x{N}x{Kd} t={transposed}: rel err {err:.3e}")
+    assert err < 3e-6
