@@ -73,8 +73,8 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.ld_tt = (long long)align_up((size_t)p.P * p.BK, 8);
     p.ld_g = p.ld_tt;
     p.ld_gt = p.ld_vt;
-    // one row partial per 64-column half tile; bf16 mode runs 256-wide pair tiles (all four written)
-    p.nb_r = (p.P == 1) ? 4 * (int)((p.BK + 255) / 256) : 2 * (int)((p.BK + BLOCK_N - 1) / BLOCK_N);
+    // one row partial per epilogue warp column part; bf16 mode runs 256-wide pair tiles (all written)
+    p.nb_r = tc::EpiRowCol::PARTS * ((p.P == 1) ? 2 * (int)((p.BK + 255) / 256) : (int)((p.BK + BLOCK_N - 1) / BLOCK_N));
     // one column partial per 128-row block; bf16 mode runs 256-row tiles (both halves are written)
     p.nb_c = (p.P == 1) ? 2 * ((B + 255) / 256) : (B + 127) / 128;
     size_t o = 0;
@@ -402,7 +402,7 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     const int tiles = ((M + MB * tc::BLOCK_M - 1) / (MB * tc::BLOCK_M)) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
     tc::GemmShape shape{M, N, Kd, chunk_iters};
-    kern<<<grid, tc::NUM_THREADS, L::TOTAL, stream>>>(ma, mb, shape, ep);
+    kern<<<grid, tc::num_threads<Epi>(), L::TOTAL, stream>>>(ma, mb, shape, ep);
     B200_LAUNCH_OK(what);
     return 0;
 }
@@ -435,7 +435,7 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     const int max_pairs = num_sms() / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
     tc::GemmShape shape{M, N, Kd, 0};
-    kern<<<2 * pairs, tc::NUM_THREADS, L::TOTAL, stream>>>(ma, mb, shape, ep);
+    kern<<<2 * pairs, tc::num_threads<Epi>(), L::TOTAL, stream>>>(ma, mb, shape, ep);
     B200_LAUNCH_OK(what);
     return 0;
 }

@@ -88,7 +88,9 @@ __device__ __forceinline__ void tcgen05_fence_before() {
 __device__ __forceinline__ void tcgen05_fence_after() {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
-__device__ __forceinline__ void epi_bar_sync();  // named barrier over the epilogue threads
+__device__ __forceinline__ void epi_bar_sync(int nthreads) {  // named barrier 1: epilogue threads only
+    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
+}
 
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar,
                                             int c0, int c1) {
@@ -192,22 +194,26 @@ __device__ __forceinline__ float fast_exp2(float x) {
 // ----------------------------------------------------------------------------
 // Epilogue context handed to the functors
 // ----------------------------------------------------------------------------
-// Eight epilogue warps: warp (q, h) owns TMEM lanes [32q, 32q+32) (= 32 output rows)
-// and the column half h of the tile, i.e. HN = BLOCK_N/2 columns per thread.
+// 4 * PARTS epilogue warps: warp (q, h) owns TMEM lanes [32q, 32q+32) (= 32 output rows)
+// and column part h of each 128-wide block, i.e. HN = 128 / PARTS columns per thread.
+// The epilogues are latency-bound straight-line code (ncu: "wait" and "long scoreboard"
+// stalls with 2 warps per scheduler), so more, shorter warps finish a tile sooner.
+// Each functor picks its own PARTS: the gradient-tile epilogue (EpiG) is fastest with 16 warps
+// (353 -> 295 us), the row+column statistics (warp-wide butterflies, fixed cost per warp) with 8.
 struct EpiCtx {
     int m0, n0;        // origin of this thread's sub-tile: row block start, FIRST COLUMN OF ITS HALF
     int m_blk, n_blk;  // tile coordinates
-    int half;          // 0 / 1: which column half
+    int half;          // 0 .. PARTS-1: which column part of the 128-wide block
+    int nthreads;      // epilogue threads of this CTA (for the named barrier)
     int M, N;          // problem extent
     int tid;           // row within the tile, 0..127
-    int etid;          // 0..255 within the epilogue warps
+    int etid;          // index within the epilogue warps
     int lane, q;       // lane, lane quarter
     int par;           // tile parity, for double-buffered smem scratch
     float *scratch;    // SCRATCH_FLOATS floats of smem shared by the epilogue warps
     uint8_t *stage;    // Epi::STAGE_BYTES bytes of smem (this warp's slice starts at warp_slot)
-    int warp_slot;     // 0..7
+    int warp_slot;     // 0 .. 4*PARTS-1
 };
-constexpr int NUM_EPI_WARPS = 8;
 constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 // Every functor receives the finished fp32 accumulator (its row, its column half) in
 // registers (acc[HN], compile-time indexed): the kernel has already drained TMEM, so
@@ -216,6 +222,7 @@ constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 // ---- plain store: C = alpha * acc (dvideo / dtext GEMMs, and the test hook) ----
 struct EpiStore {
     static constexpr int STAGE_BYTES = 0;
+    static constexpr int PARTS = 2;
     struct Params {
         float *C;
         long long ldc;
@@ -251,7 +258,7 @@ struct EpiStore {
 };
 
 // ---- row AND column log-sum-exp of the tile (MIL-NCE forward; loss.py:16-17) ----
-// part_row[2*n_blk + half][row] = log sum_{n in half tile} exp(s[row, n])     s = scale * acc
+// part_row[PARTS*n_blk + part][row] = log sum_{n in part} exp(s[row, n])   s = scale * acc
 // part_col[m_blk][col]          = log sum_{m in tile} exp(s[m, col])          (natural logs)
 // One exp per element serves both statistics: e = 2^(y - wmax) with wmax the maximum over
 // the warp's 32 x HN sub-tile.  Row sums are thread-local; column sums need a reduction
@@ -283,6 +290,7 @@ constexpr float TINY_SUM = 7.8886090522101181e-31f;  // 2^-100
 
 struct EpiRowCol {
     static constexpr int STAGE_BYTES = 0;
+    static constexpr int PARTS = 2;
     struct Params {
         float *part_row;  // may be null: skip the row statistic
         long long ldr;
@@ -292,7 +300,7 @@ struct EpiRowCol {
     };
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
-        static_assert(HN == 64, "scratch layout assumes 128-wide tiles");
+        static_assert(HN * PARTS == 128, "scratch layout assumes 128-wide column blocks");
         const float sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
         const int lane = c.lane;
         const int row = c.m0 + c.tid;
@@ -355,14 +363,14 @@ struct EpiRowCol {
             for (int ch = 0; ch < HN / 32; ++ch) wl[ch] = -INFINITY;
         }
         if (p.part_row != nullptr && row_ok)
-            p.part_row[(long long)(c.n_blk * 2 + c.half) * p.ldr + row] = row_lse * LN2;
+            p.part_row[(long long)(c.n_blk * PARTS + c.half) * p.ldr + row] = row_lse * LN2;
         if (want_col) {
             // merge the four lane-quarters' partials through smem (double-buffered by tile parity)
             float *buf = c.scratch + c.par * (4 * 128);
 #pragma unroll
             for (int ch = 0; ch < HN / 32; ++ch)
                 buf[c.q * 128 + c.half * HN + ch * 32 + lane] = wl[ch];
-            epi_bar_sync();
+            epi_bar_sync(c.nthreads);
             if (c.etid < 128) {
                 const float v0 = buf[c.etid], v1 = buf[128 + c.etid], v2 = buf[256 + c.etid],
                             v3 = buf[384 + c.etid];
@@ -395,7 +403,8 @@ struct GFast {
     const float *mid_log2_dev;
 };
 struct EpiG {
-    static constexpr int STAGE_BYTES = NUM_EPI_WARPS * 32 * 64 * 2;  // 32 KB
+    static constexpr int STAGE_BYTES = 4 * 32 * 128 * 2;  // 32 KB: a 128 x 128 fp16 block
+    static constexpr int PARTS = 4;
     struct Params {
         const float *den;  // all B entries
         const float *nom;
@@ -407,26 +416,32 @@ struct EpiG {
         const float *scale_dev;
         GFast fast;
     };
-    // write this warp's 32 x 64 fp16 sub-tile held in `vals` (already scaled) to dst planes
+    // write this warp's 32 x HN fp16 sub-tile (already scaled, packed) to one plane of `out`
     template <int HN>
     __device__ static void store_plane(const EpiCtx &c, uint8_t *wstage, const uint32_t (&packed)[HN / 2],
                                        __half *out, long long ldo) {
-        // stage: row r = lane, 8 chunks of 16 B (8 halves); chunk k stored at k ^ (r & 7)
+        constexpr int CH = HN / 8;        // 16-byte chunks per row (8 or 4)
+        constexpr int ROWB = HN * 2;      // bytes per staged row (128 or 64)
+        constexpr int RPI = 32 / CH;      // rows covered by one write-out instruction (4 or 8)
+        // stage: row r = lane; chunk k is stored at a rotated position so that the eight lanes of a
+        // shared-memory phase hit different banks (rows 128 B apart: k ^ (r & 7); 64 B: k ^ ((r>>1)&3))
         const int r = c.lane;
+        const int rot = (CH == 8) ? (r & 7) : ((r >> 1) & 3);
 #pragma unroll
-        for (int k = 0; k < HN / 8; ++k) {
+        for (int k = 0; k < CH; ++k) {
             uint4 v = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
-            *reinterpret_cast<uint4 *>(wstage + r * 128 + ((k ^ (r & 7)) << 4)) = v;
+            *reinterpret_cast<uint4 *>(wstage + r * ROWB + ((k ^ rot) << 4)) = v;
         }
         __syncwarp();
-        // write-out: each instruction covers 4 rows x 128 B; lane -> (row = it*4 + lane/8, chunk = lane%8)
-        const int sub = c.lane >> 3, k = c.lane & 7;
+        // write-out: lane -> (row = it*RPI + lane/CH, chunk = lane%CH): full 16-byte chunks, RPI rows
+        const int sub = c.lane / CH, k = c.lane % CH;
         const int col = c.n0 + k * 8;
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {
-            const int rr = it * 4 + sub;
+        for (int it = 0; it < CH; ++it) {
+            const int rr = it * RPI + sub;
             const int grow = c.m0 + c.q * 32 + rr;
-            const uint4 v = *reinterpret_cast<const uint4 *>(wstage + rr * 128 + ((k ^ (rr & 7)) << 4));
+            const int rrot = (CH == 8) ? (rr & 7) : ((rr >> 1) & 3);
+            const uint4 v = *reinterpret_cast<const uint4 *>(wstage + rr * ROWB + ((k ^ rrot) << 4));
             if (grow < c.M) {
                 __half *dst = out + (long long)grow * ldo + col;
                 if (col + 8 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
@@ -443,12 +458,15 @@ struct EpiG {
     }
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
-        static_assert(HN == 64, "staging layout assumes 64 columns per warp");
+        static_assert(HN == 64 || HN == 32, "staging layout: 64 or 32 columns per warp");
         const bool fast = __ldg(p.fast.flag_dev) != 0;
         const float mid = __ldg(p.fast.mid_log2_dev);
-        float *tab = c.scratch + c.par * 128;  // per column of the 128-wide tile
-        if (c.etid < 128) {
-            const int n = c.n_blk * 128 + c.etid;
+        // per-column factors of this warp's 64 columns, in the warp's own 256 bytes of smem:
+        // no CTA-wide barrier (a shared table made all eight warps wait for the slowest den load)
+        float *tab = c.scratch + c.warp_slot * HN;
+#pragma unroll
+        for (int h = 0; h < HN / 32; ++h) {
+            const int n = c.n0 + h * 32 + c.lane;
             float t;
             if (n < c.N) {
                 const float dc = __ldg(p.den + (p.col_off + n) / p.cdiv) * LOG2E;
@@ -456,10 +474,9 @@ struct EpiG {
             } else {
                 t = fast ? 0.f : INFINITY;  // masked column (never stored)
             }
-            tab[c.etid] = t;
+            tab[h * 32 + c.lane] = t;
         }
-        epi_bar_sync();
-        tab += c.half * HN;
+        __syncwarp();
         const float sc = __ldg(p.scale_dev) * LOG2E;
         const int row = c.m0 + c.tid;
         const int rs = (p.row_off + min(row, c.M - 1)) / p.rdiv;
@@ -498,8 +515,9 @@ struct EpiG {
                 acc[i] = g * G_SCALE;
             }
         }
+        __syncwarp();             // all lanes are done with this run's table
         if (c.n0 >= c.N) return;  // warp-uniform: nothing of this half is inside the matrix
-        uint8_t *wstage = c.stage + c.warp_slot * (32 * 64 * 2);
+        uint8_t *wstage = c.stage + c.warp_slot * (32 * HN * 2);
         uint32_t hi[HN / 2];
 #pragma unroll
         for (int i = 0; i < HN / 2; ++i) {
@@ -535,18 +553,16 @@ struct GemmShape {
     int chunk_iters;
 };
 
-constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;  // TMA warp + MMA warp + 8 epilogue warps
-constexpr int NUM_EPI_THREADS = NUM_EPI_WARPS * 32;
-__device__ __forceinline__ void epi_bar_sync() {  // named barrier 1: the epilogue threads only
-    asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory");
-}
+// threads per CTA: TMA warp + MMA warp + 4 * PARTS epilogue warps
+template <class Epi>
+constexpr int num_threads() { return 64 + 4 * Epi::PARTS * 32; }
 
 template <int BLOCK_N, int EPI_STAGE_BYTES, int MB>
 struct SmemLayout {
     static constexpr int A_BYTES = MB * BLOCK_M * BLOCK_K * 2;  // MB row blocks of 128
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int TAIL_BYTES = 8192;  // barriers, tmem slot, epilogue scratch
+    static constexpr int TAIL_BYTES = 8192;  // barriers, tmem slot, epilogue scratch (SCRATCH_FLOATS)
     static constexpr int MAX_SMEM = 232448;  // 227 KB
     static constexpr int STAGES_FIT = (MAX_SMEM - 1024 - TAIL_BYTES - EPI_STAGE_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
@@ -567,12 +583,13 @@ struct SmemLayout {
 //               (CTAs in flight share the A rows - for skinny N this keeps a huge A from being
 //               streamed from HBM once per n-block).
 template <int BLOCK_N, class Epi, bool A_MN = false, int MB = 1, bool N_FAST = false>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(num_threads<Epi>(), 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const GemmShape shape, const typename Epi::Params ep) {
     using L = SmemLayout<BLOCK_N, Epi::STAGE_BYTES, MB>;
     constexpr int STAGES = L::STAGES;
-    constexpr int HN = BLOCK_N / 2;
+    constexpr int HN = BLOCK_N / Epi::PARTS;
+    constexpr int NUM_EPI_WARPS = 4 * Epi::PARTS;
     constexpr int TILE_M = MB * BLOCK_M;
     constexpr int ACC_COLS = MB * BLOCK_N;  // TMEM columns per accumulator buffer
     constexpr uint32_t TMEM_COLS = (2 * ACC_COLS <= 256) ? 256 : 512;
@@ -719,6 +736,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
         c.stage = epi_stage;
+        c.nthreads = NUM_EPI_WARPS * 32;
         uint32_t cc = 0;
         int runs = 0;  // epilogue invocations so far (parity of the smem scratch buffers)
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {

@@ -95,18 +95,22 @@ struct SmemLayout2 {
     static constexpr int TAIL_BYTES = 8192;
     static constexpr int MAX_SMEM = 232448;
     static constexpr int STAGES_FIT = (MAX_SMEM - 1024 - TAIL_BYTES - EPI_STAGE_BYTES) / STAGE_BYTES;
-    static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
+    // epilogues that read per-sample vectors from global memory (EPI_STAGE_BYTES > 0: EpiG) keep
+    // the ring at 4 stages so that ~55 KB of the SM stay L1 cache and those reads hit
+    static constexpr int STAGES_MAX = EPI_STAGE_BYTES > 0 ? 4 : 6;
+    static constexpr int STAGES = STAGES_FIT > STAGES_MAX ? STAGES_MAX : STAGES_FIT;
     static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + TAIL_BYTES + 1024;
     static_assert(STAGES >= 3, "pipeline too shallow");
 };
 
 template <class Epi, bool A_MN = false, bool N_FAST = false>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(num_threads<Epi>(), 1)
 gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmShape shape, const typename Epi::Params ep) {
     using L = SmemLayout2<Epi::STAGE_BYTES>;
     constexpr int STAGES = L::STAGES;
-    constexpr int HN = 64;                 // columns per epilogue thread per pass
+    constexpr int HN = 128 / Epi::PARTS;   // columns per epilogue thread per pass
+    constexpr int NUM_EPI_WARPS = 4 * Epi::PARTS;
     constexpr uint32_t TMEM_COLS = 512;    // 2 buffers x 256 columns
 
     extern __shared__ uint8_t smem_raw[];
@@ -233,6 +237,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
         c.stage = epi_stage;
+        c.nthreads = NUM_EPI_WARPS * 32;
         uint32_t cc = 0;
         int runs = 0;
         for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
