@@ -192,6 +192,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # the JSON line must be the only thing on stdout: NCCL_DEBUG=VERSION prints a banner there
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -270,7 +273,8 @@ def run_b200(args):
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"MILNCELoss fwd+bwd B={B} K={K} D={D} (BASELINE configs[1])",
                    "global_batch": B, "candidates": K, "dim": D,
-                   "parallelism": f"dp{world} batch-sharded, NCCL all-gather of embeddings" if world > 1 else "single GPU",
+                   "parallelism": (f"dp{world}: batch sharded over ranks, NCCL all-gather of the embeddings, each rank "
+                                   f"computes its rows of S, reduce-scatter of the text gradient") if world > 1 else "single GPU",
                    "l2": "per-step working set (fp16 G and G^T, ~1.1 GB) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,

@@ -78,6 +78,28 @@ int milnce_backward(const void *video, const void *text, const float *den, const
                     int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
                     void *workspace, size_t workspace_bytes, void *stream);
 
+/* Rows-only sharding (bfloat16 inputs; i0 and D multiples of 8): the multi-GPU scheme that
+ * GatheredMILNCELoss uses by default.  Same inputs as above (all-gathered video/text, a range),
+ * but a rank computes only the rows of the similarity matrix it owns - 4/W GEMM units per rank
+ * instead of 6/W - at the price of one reduce-scatter.  Replaces the same reference code as
+ * milnce_forward/backward (loss.py:10-18, utils.py:11-24).
+ *   forward : row_lse[i0, i0+n)  = log sum over ALL text columns of exp(S[i, :])      (complete)
+ *             col_part[0, B)     = log sum over the OWNED rows i and the K candidates of sample j
+ *                                  of exp(S[i, jK+k])   (partial: combine over ranks with logsumexp)
+ *             nom[i0, i0+n)      as in milnce_forward
+ *             The caller all-gathers row_lse / nom, logsumexp-reduces col_part over ranks and forms
+ *             den_j = logaddexp(row_lse_j, col_j), loss = mean(den - nom).
+ *   backward: dvideo (n, D) complete for the owned rows; dtext_partial (B*K, D) float32 holds only
+ *             the owned rows' contribution: reduce-scatter (sum) it over ranks to obtain each
+ *             rank's (n*K, D) slice. */
+int milnce_forward_shard(const void *video, const void *text, int B, int K, int D, int dtype,
+                         int i0, int n, float *row_lse, float *col_part, float *nom,
+                         void *workspace, size_t workspace_bytes, void *stream);
+int milnce_backward_shard(const void *video, const void *text, const float *den, const float *nom,
+                          const float *grad_loss, float *dvideo, float *dtext_partial,
+                          int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------------------------
  * soft-DTW: replaces SoftDTW.forward's distance function + _SoftDTWCUDA
  * (reference soft_dtw_cuda.py:326-363, 115-175, kernels :34-112).

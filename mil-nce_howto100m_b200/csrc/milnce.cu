@@ -54,6 +54,7 @@ struct Plan {
     long long ld_g, ld_gt;   // G (n, P*BK), Gt (n*K, P*B)
     long long ld_g2;         // G2 (B, n*K) for the sharded bf16 backward
     int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
+    int nb_cl;               // 128-row blocks of the owned rows
     int chunk_s, chunk_g;    // k-blocks per tensor-core accumulation chunk (S passes / grad GEMMs)
     size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_g, off_gt, total;
 };
@@ -85,7 +86,8 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.off_vt = take((size_t)D * p.ld_vt * 2);
     p.off_tt = take((size_t)D * p.ld_tt * 2);
     p.off_pr = take((size_t)p.nb_r * n * 4);
-    p.off_pc = take((size_t)p.nb_c * n * K * 4);
+    p.nb_cl = 2 * ((n + 255) / 256);  // row blocks of the owned rows (rows-only sharding)
+    p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) * 4);
     p.off_diff = take((size_t)n * 4 * 2);  // den - nom, then the merged den
     p.off_g = take((size_t)n * p.ld_g * 2);
     // P == 3: G^T (n*K, P*B) from the transposed pass.  P == 1: G2 = G[all rows, own columns]
@@ -347,10 +349,12 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
     }
     if (lane == 0) {
         const float nm = pm + logf(ps);
-        const float dn = rowcol[w];
-        den[i] = dn;
         nom[i] = nm;
-        diff[w] = dn - nm;
+        if (rowcol != nullptr) {  // (null: rows-only sharding, den is formed after the exchange)
+            const float dn = rowcol[w];
+            den[i] = dn;
+            diff[w] = dn - nm;
+        }
     }
 }
 
@@ -607,6 +611,81 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     return rc;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Rows-only sharding (bf16 inputs): a rank computes ONLY the rows of S it owns.
+//   forward : row_lse of its samples (complete) and, for EVERY sample j, the partial column
+//             statistic over its own rows; ranks exchange those (B floats each) and form den.
+//   backward: G[own rows, :] -> dvideo (own rows, complete) and a (B*K, D) PARTIAL dtext that the
+//             caller reduce-scatters.  4/W GEMM units per rank instead of 6/W for the row+column
+//             block scheme of milnce_forward/backward with n < B.
+// ---------------------------------------------------------------------------------------------
+int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
+                       float *row_lse, float *col_part, float *nom, uint8_t *ws, cudaStream_t st) {
+    int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st);
+    if (rc) return rc;
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
+    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    float *pr = reinterpret_cast<float *>(ws + p.off_pr);
+    float *pc = reinterpret_cast<float *>(ws + p.off_pc);
+    tc::EpiRowCol::Params e{pr, (long long)p.n, pc, (long long)p.BK, &sc->inv_ss};
+    rc = launch_gemm2<tc::EpiRowCol>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK,
+                                     p.D, e, st, "milnce forward (rows-only shard)");
+    if (rc) return rc;
+    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, p.K, p.n, p.nb_r, 0,
+                                                            row_lse + p.i0);
+    merge_partials_kernel<<<(p.B + 31) / 32, 1024, 0, st>>>(nullptr, pc, p.K, p.B, 0, p.nb_cl, col_part);
+    const int warps_per_block = 8;
+    finalize_kernel<__nv_bfloat16><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32,
+                                     0, st>>>(video, text, nullptr, p.K, p.D, p.i0, p.n, nullptr, nom,
+                                              nullptr);
+    B200_LAUNCH_OK("milnce shard finalize");
+    return 0;
+}
+
+int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
+                        const float *den, const float *nom, const float *grad_loss, float *dvideo,
+                        float *dtext_partial, int reuse, uint8_t *ws, cudaStream_t st) {
+    int rc;
+    if (!reuse) {
+        rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st);
+        if (rc) return rc;
+    }
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    scalars_backward_kernel<<<1, 1024, 0, st>>>(sc, grad_loss, den, p.B);
+    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
+    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
+    const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
+    __half *g = reinterpret_cast<__half *>(ws + p.off_g);
+    const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, 1, 0, p.K, &sc->inv_ss, fast};
+    rc = launch_gemm2<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
+                                st, "milnce backward (rows-only shard) G");
+    if (rc) return rc;
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
+    rc = launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+                                                 "milnce dvideo GEMM (shard)");
+    if (rc) return rc;
+    // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
+    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext};
+    return launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd,
+                                                  st, "milnce partial dtext GEMM (shard)");
+}
+
+int check_shard(const Plan &p, int dtype) {
+    if (dtype != B200HEAD_BF16) {
+        b200::set_error("rows-only sharding is implemented for bfloat16 inputs; use "
+                        "milnce_forward/milnce_backward with a range for float32");
+        return B200HEAD_ERR_ARG;
+    }
+    if (p.i0 % 8 != 0 || p.D % 8 != 0) {
+        b200::set_error("rows-only sharding needs i0 and D to be multiples of 8 (TMA alignment)");
+        return B200HEAD_ERR_ARG;
+    }
+    return 0;
+}
+
 }  // namespace
 
 extern "C" size_t milnce_workspace_bytes(int B, int K, int D, int dtype, int n) {
@@ -707,4 +786,51 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
                                                                  (cudaStream_t)stream, "gemm2 test hook")
                         : launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep,
                                                                    (cudaStream_t)stream, "gemm2 test hook");
+}
+
+extern "C" int milnce_forward_shard(const void *video, const void *text, int B, int K, int D, int dtype,
+                                    int i0, int n, float *row_lse, float *col_part, float *nom,
+                                    void *workspace, size_t workspace_bytes, void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, dtype == B200HEAD_BF16 ? dtype : B200HEAD_BF16, i0, n)) {
+        b200::set_error("milnce_forward_shard: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!video || !text || !row_lse || !col_part || !nom) {
+        b200::set_error("milnce_forward_shard: null pointer argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = check_shard(p, dtype);
+    if (rc) return rc;
+    rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    return forward_shard_impl(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text, row_lse,
+                              col_part, nom, (uint8_t *)workspace, (cudaStream_t)stream);
+}
+
+extern "C" int milnce_backward_shard(const void *video, const void *text, const float *den,
+                                     const float *nom, const float *grad_loss, float *dvideo,
+                                     float *dtext_partial, int B, int K, int D, int dtype, int i0, int n,
+                                     int reuse_forward_ws, void *workspace, size_t workspace_bytes,
+                                     void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, dtype == B200HEAD_BF16 ? dtype : B200HEAD_BF16, i0, n)) {
+        b200::set_error("milnce_backward_shard: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!video || !text || !den || !nom || !grad_loss || !dvideo || !dtext_partial) {
+        b200::set_error("milnce_backward_shard: null pointer argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = check_shard(p, dtype);
+    if (rc) return rc;
+    rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    return backward_shard_impl(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text, den, nom,
+                               grad_loss, dvideo, dtext_partial, reuse_forward_ws, (uint8_t *)workspace,
+                               (cudaStream_t)stream);
 }

@@ -72,6 +72,53 @@ class CudaBackend:
         return dv, dt
 
 
+    # ---- rows-only sharding (bf16): see include/b200head.h, milnce_forward_shard ----
+    @staticmethod
+    def supports_rows_scheme(video, i0):
+        return video.dtype == torch.bfloat16 and i0 % 8 == 0 and video.shape[1] % 8 == 0
+
+    @staticmethod
+    def forward_shard(video, text, i0, n):
+        """Returns (row_lse[B] (own entries valid), col_part[B], nom[B] (own entries valid), ws)."""
+        lib = _lib.load()
+        B, D = video.shape
+        K = text.shape[0] // B
+        code = _dtype_code(video)
+        dev = video.device
+        nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        row = torch.empty(B, dtype=torch.float32, device=dev)
+        colp = torch.empty(B, dtype=torch.float32, device=dev)
+        nom = torch.empty(B, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_forward_shard(_ptr(video), _ptr(text), B, K, D, code, i0, n, _ptr(row),
+                                          _ptr(colp), _ptr(nom), _ptr(ws), nbytes, _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_forward_shard")
+        return row, colp, nom, ws
+
+    @staticmethod
+    def backward_shard(video, text, den, nom, grad_loss, i0, n, ws):
+        """Returns float32 (dvideo (n, D), dtext_partial (B*K, D)); the latter is to be reduce-scattered."""
+        lib = _lib.load()
+        B, D = video.shape
+        K = text.shape[0] // B
+        code = _dtype_code(video)
+        dev = video.device
+        reuse = 1
+        if ws is None:
+            nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            reuse = 0
+        dv = torch.empty(n, D, dtype=torch.float32, device=dev)
+        dtp = torch.empty(B * K, D, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_backward_shard(_ptr(video), _ptr(text), _ptr(den), _ptr(nom), _ptr(grad_loss),
+                                           _ptr(dv), _ptr(dtp), B, K, D, code, i0, n, reuse, _ptr(ws),
+                                           ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_backward_shard")
+        return dv, dtp
+
+
 def _validate(video_embd, text_embd):
     if video_embd.dim() != 2 or text_embd.dim() != 2:
         raise ValueError("video_embd must be (B, D) and text_embd (B*K, D)")

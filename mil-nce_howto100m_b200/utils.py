@@ -90,6 +90,55 @@ class _GatheredMILNCE(torch.autograd.Function):
         return dv.to(vdt), dt.to(tdt), None, None, None, None
 
 
+class _GatheredMILNCERows(torch.autograd.Function):
+    """Rows-only sharding: each rank computes only its rows of the similarity matrix.
+
+    Exchanges: all-gather of the embeddings (as in the reference), one all-gather of
+    2*b + B floats per rank (row statistic, positives, partial column statistic) and one
+    reduce-scatter of the (B*K, D) float32 partial text gradient in backward.  Per-rank GEMM
+    work is 4/W of the single-GPU step (6/W for the row+column block scheme above)."""
+
+    @staticmethod
+    def forward(ctx, video_local, text_local, world, rank, group, backend):
+        b = video_local.shape[0]
+        v = video_local.detach().contiguous()
+        t = text_local.detach().contiguous()
+        V = torch.empty((world * b, v.shape[1]), dtype=v.dtype, device=v.device)
+        T = torch.empty((world * t.shape[0], t.shape[1]), dtype=t.dtype, device=t.device)
+        h1 = dist.all_gather_into_tensor(V, v, group=group, async_op=True)
+        h2 = dist.all_gather_into_tensor(T, t, group=group, async_op=True)
+        h1.wait()
+        h2.wait()
+        B = world * b
+        i0 = rank * b
+        row, colp, nom, ws = backend.forward_shard(V, T, i0, b)
+        # one small all-gather: [row_lse of my samples | nom of my samples | my column partials]
+        pack = torch.cat([row[i0:i0 + b], nom[i0:i0 + b], colp]).contiguous()
+        allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
+        dist.all_gather_into_tensor(allp, pack, group=group)
+        allp = allp.view(world, 2 * b + B)
+        row_all = allp[:, :b].reshape(B)
+        nom_all = allp[:, b:2 * b].reshape(B).contiguous()
+        col_all = torch.logsumexp(allp[:, 2 * b:], dim=0)
+        den = torch.logaddexp(row_all, col_all).contiguous()
+        loss = (den - nom_all).mean()
+        ctx.save_for_backward(V, T, den, nom_all)
+        ctx.ws = ws
+        ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0])
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        V, T, den, nom = ctx.saved_tensors
+        i0, b, backend, vdt, tdt, group, bk_local = ctx.meta
+        g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
+        dv, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws)
+        ctx.ws = None
+        dt = torch.empty((bk_local, dt_partial.shape[1]), dtype=dt_partial.dtype, device=dt_partial.device)
+        dist.reduce_scatter_tensor(dt, dt_partial, op=dist.ReduceOp.SUM, group=group)
+        return dv.to(vdt), dt.to(tdt), None, None, None, None
+
+
 class GatheredMILNCELoss(torch.nn.Module):
     """allgather(video), allgather(text), MILNCELoss - fused and sharded.
 
@@ -99,11 +148,17 @@ class GatheredMILNCELoss(torch.nn.Module):
     embeddings of this rank.
     """
 
-    def __init__(self, args=None, group=None, backend=None):
+    def __init__(self, args=None, group=None, backend=None, scheme="auto"):
+        """scheme: "rows" (each rank computes only its rows of S, reduce-scatter of the text
+        gradient; bf16 embeddings), "rowcol" (row block + column block per rank, no gradient
+        collective - the reference's communication pattern), or "auto" (rows when available)."""
         super().__init__()
+        if scheme not in ("auto", "rows", "rowcol"):
+            raise ValueError("scheme must be 'auto', 'rows' or 'rowcol'")
         self.args = args
         self.group = group
         self._backend = backend
+        self.scheme = scheme
 
     def forward(self, video_embd, text_embd):
         from .loss import CudaBackend, _validate
@@ -112,4 +167,12 @@ class GatheredMILNCELoss(torch.nn.Module):
             _validate(video_embd, text_embd)
             backend = CudaBackend
         world, rank = _world(self.args)
-        return _GatheredMILNCE.apply(video_embd, text_embd, world, rank, self.group, backend)
+        use_rows = False
+        if world > 1 and self.scheme != "rowcol":
+            ok = backend.supports_rows_scheme(video_embd, rank * video_embd.shape[0])
+            if self.scheme == "rows" and not ok:
+                raise RuntimeError("scheme='rows' needs bfloat16 embeddings and a local batch that is a "
+                                   "multiple of 8")
+            use_rows = ok
+        fn = _GatheredMILNCERows if use_rows else _GatheredMILNCE
+        return fn.apply(video_embd, text_embd, world, rank, self.group, backend)

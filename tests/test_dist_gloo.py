@@ -63,6 +63,43 @@ class OracleBackend:
         return torch.from_numpy(dv), torch.from_numpy(dt)
 
 
+    # ---- rows-only sharding (include/b200head.h: milnce_forward_shard / milnce_backward_shard) ----
+    @staticmethod
+    def supports_rows_scheme(video, i0):
+        return True
+
+    @staticmethod
+    def forward_shard(V, T, i0, n):
+        from oracle import milnce_oracle
+        B = V.shape[0]
+        x, nom, _ = milnce_oracle.milnce_stats(V.double().numpy(), T.double().numpy())
+        K = x.shape[2]
+        row = np.full(B, np.nan)
+        nm = np.full(B, np.nan)
+        row[i0:i0 + n] = milnce_oracle._lse(x[i0:i0 + n].reshape(n, B * K), axis=1)
+        nm[i0:i0 + n] = nom[i0:i0 + n]
+        # partial column statistic over the OWNED rows only, for every sample j
+        colp = milnce_oracle._lse(np.transpose(x[i0:i0 + n], (1, 0, 2)).reshape(B, n * K), axis=1)
+        return torch.from_numpy(row), torch.from_numpy(colp), torch.from_numpy(nm), None
+
+    @staticmethod
+    def backward_shard(V, T, den, nom, g, i0, n, ws):
+        v = V.double().numpy()
+        t = T.double().numpy()
+        B = v.shape[0]
+        K = t.shape[0] // B
+        den = den.numpy()
+        nom = nom.numpy()
+        assert not np.isnan(den).any()
+        x = (v @ t.T).reshape(B, B, K)
+        rows = slice(i0, i0 + n)
+        g_r = np.exp(x[rows] - den[rows, None, None]) + np.exp(x[rows] - den[None, :, None])
+        for r in range(n):
+            g_r[r, i0 + r, :] -= np.exp(x[i0 + r, i0 + r, :] - nom[i0 + r])
+        g_r = (float(g[0]) / B) * g_r.reshape(n, B * K)
+        return torch.from_numpy(g_r @ t), torch.from_numpy(g_r.T @ v[rows])
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -71,7 +108,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, b, K, D, out):
+def _worker(rank, world, port, b, K, D, scheme, out):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -99,7 +136,7 @@ def _worker(rank, world, port, b, K, D, out):
         v_loc.grad = None
 
         # 2. sharded loss == reference loss on gathered tensors, grads == local slices
-        mod = milnce_b200.GatheredMILNCELoss(args=args, backend=OracleBackend)
+        mod = milnce_b200.GatheredMILNCELoss(args=args, backend=OracleBackend, scheme=scheme)
         loss = mod(v_loc, t_loc)
         (loss * 1.75).backward()  # 1.75 is exact in float32 (grad_loss is passed as fp32)
         ref_loss, ref_dv, ref_dt, _, _ = milnce_oracle.milnce_closed_form(V.numpy(), T.numpy(), 1.75)
@@ -112,11 +149,12 @@ def _worker(rank, world, port, b, K, D, out):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("scheme", ["rowcol", "rows"])
 @pytest.mark.parametrize("world", [2, 4])
-def test_gathered_loss_world(world):
+def test_gathered_loss_world(world, scheme):
     port = _free_port()
     out = mp.get_context("spawn").Array("i", [0] * world)
-    mp.spawn(_worker, args=(world, port, 3, 2, 8, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, 3, 2, 8, scheme, out), nprocs=world, join=True)
     assert list(out) == [1] * world
 
 

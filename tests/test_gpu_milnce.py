@@ -165,3 +165,32 @@ def test_full_size_config(dtype):
     e_dt = ((dt.double() - td.grad).norm() / td.grad.norm()).item()
     print(f"full size {dtype}: loss {e_loss:.2e} dV {e_dv:.2e} dT {e_dt:.2e}")
     assert e_loss < tol and e_dv < tol and e_dt < tol
+
+
+def test_rows_only_sharding_emulated_on_one_gpu():
+    """milnce_forward_shard / milnce_backward_shard for four emulated ranks: merged statistics equal
+    the single-GPU ones, the partial text gradients sum to the full one (what reduce-scatter does)."""
+    B, K, D, W = 1024, 4, 512, 4
+    g = torch.Generator().manual_seed(21)
+    v = (torch.randn(B, D, generator=g) * 0.2).bfloat16().cuda()
+    t = (torch.randn(B * K, D, generator=g) * 0.2).bfloat16().cuda()
+    loss, dv, dt, den, nom = _raw(v, t)
+    b = B // W
+    outs = [CudaBackend.forward_shard(v, t, r * b, b) for r in range(W)]
+    row_all = torch.cat([o[0][r * b:(r + 1) * b] for r, o in enumerate(outs)])
+    nom_all = torch.cat([o[2][r * b:(r + 1) * b] for r, o in enumerate(outs)])
+    col_all = torch.logsumexp(torch.stack([o[1] for o in outs]), dim=0)
+    den_all = torch.logaddexp(row_all, col_all)
+    assert torch.allclose(den_all, den, rtol=2e-6, atol=0)
+    assert torch.allclose(nom_all, nom, rtol=1e-6, atol=0)
+    one = torch.ones(1, device="cuda")
+    dt_sum = torch.zeros_like(dt)
+    for r, o in enumerate(outs):
+        dvr, dtp = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[3])
+        assert rel_err(dvr.cpu().numpy(), dv[r * b:(r + 1) * b].cpu().numpy()) < 5e-6
+        dt_sum += dtp
+    assert rel_err(dt_sum.cpu().numpy(), dt.cpu().numpy()) < 5e-6
+    lib = milnce_b200._lib.load()
+    # float32 inputs are rejected with a clear message (they use the row+column block scheme)
+    with pytest.raises(RuntimeError, match="bfloat16"):
+        CudaBackend.forward_shard(v.float(), t.float(), 0, b)

@@ -25,7 +25,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, scheme, out):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -40,7 +40,7 @@ def _worker(rank, world, port, out):
         T = (torch.randn(B * K, D, generator=g) * 0.1).bfloat16().cuda()
         v_loc = V[rank * b:(rank + 1) * b].clone().requires_grad_(True)
         t_loc = T[rank * b * K:(rank + 1) * b * K].clone().requires_grad_(True)
-        loss = milnce_b200.GatheredMILNCELoss()(v_loc, t_loc)
+        loss = milnce_b200.GatheredMILNCELoss(scheme=scheme)(v_loc, t_loc)
         loss.backward()
         Vf = V.clone().requires_grad_(True)
         Tf = T.clone().requires_grad_(True)
@@ -61,8 +61,9 @@ def _worker(rank, world, port, out):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_gathered_loss_two_gpus_nccl():
+@pytest.mark.parametrize("scheme", ["rows", "rowcol"])
+def test_gathered_loss_two_gpus_nccl(scheme):
     world = 2
     out = mp.get_context("spawn").Array("i", [0] * world)
-    mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), scheme, out), nprocs=world, join=True)
     assert list(out) == [1] * world
