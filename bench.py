@@ -7,8 +7,9 @@ Headline metric: MIL-NCE forward+backward similarity-pairs/s at global batch
 B=8192, K=4, D=512 (BASELINE.json configs[1]; pairs per step = B * B*K).  One
 "step" = one forward + one backward of the loss on one batch of synthetic
 embeddings.  At N > 1 GPUs the global batch is sharded over ranks (configs[3]),
-embeddings are all-gathered with NCCL, and each rank computes only its row and
-column block (strong scaling: total work fixed).
+embeddings are all-gathered with NCCL, each rank computes only its rows of the
+similarity matrix and the text gradient is reduce-scattered (strong scaling: total
+work fixed).
 
 One JSON line is printed by rank 0.  Besides the contract keys it carries
   roofline      tensor-pipe roofline of the step (algorithmic 6*B*BK*D FLOP)
@@ -191,10 +192,12 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # The JSON line must be the only thing on stdout, and NCCL prints its version banner there:
+    # send fd 1 to stderr while the job runs and restore it just before the line is printed.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # the JSON line must be the only thing on stdout: NCCL_DEBUG=VERSION prints a banner there
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -275,11 +278,11 @@ def run_b200(args):
                    "global_batch": B, "candidates": K, "dim": D,
                    "parallelism": (f"dp{world}: batch sharded over ranks, NCCL all-gather of the embeddings, each rank "
                                    f"computes its rows of S, reduce-scatter of the text gradient") if world > 1 else "single GPU",
-                   "l2": "per-step working set (fp16 G and G^T, ~1.1 GB) exceeds the 126 MB L2; no explicit flush"},
+                   "l2": "per-step working set (fp16 G, 0.54 GB written and read twice) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3},
-        "gpu_launches": 14 * (args.steps),
+        "gpu_launches": 13 * (args.steps),
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
@@ -297,9 +300,13 @@ def run_b200(args):
         line["cpu_baseline"] = {
             "value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
             "sample": f"B={bs} of {B}, K={K}, D={D}, fp32, torch CPU port of loss.py:10-18, 5 steps, {s * 1e3:.0f} ms/step"}
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        os.dup2(2, 1)
         dist.destroy_process_group()
 
 

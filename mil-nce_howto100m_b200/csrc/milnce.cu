@@ -7,15 +7,21 @@
 //   stage   video/text -> fp16 operands (power-of-two scaled; fp32 inputs are
 //           split into hi+lo fp16 planes concatenated along K so that three
 //           tensor-core products reproduce the fp32 dot product to ~2^-22)
-//   pass R  S[range, :]   = V[range] . T^T   -> per-tile row log-sum-exp
-//   pass C  S^T[range*K,:] = T[range*K] . V^T -> per-tile row log-sum-exp
-//           (the column statistic of loss.py:16 as a row statistic of S^T)
-//   final   row_i, col_i, nom_i (exact fp32 dots), den_i = logaddexp(row_i, col_i),
-//           loss = sum(den - nom) / B
+//   stats   S[range, :] = V[range] . T^T on the tensor cores; the epilogue
+//           (EpiRowCol) reduces each tile to row AND column log-sum-exp
+//           partials, S itself is never stored.  bf16 inputs use the CTA-pair
+//           kernel (tc_gemm2.cuh), fp32 inputs the chunked one-CTA kernel.
+//           With n < B (row + column sharding) a second GEMM over the column
+//           block S[:, range*K] supplies the column statistic.
+//   final   merge the partials, nom_i (exact fp32 dots),
+//           den_i = logaddexp(row_i, col_i), loss = sum(den - nom) / B
 // Backward (closed form):
-//   pass R  recompute S tile -> G  (n, B*K)  fp16 (x 2^13)     [never fp32, never S]
-//   pass C  recompute S^T tile -> G^T (n*K, B)
-//   dvideo = G . T, dtext = G^T . V  (two more tcgen05 GEMMs, fp32 out)
+//   G       recompute the S tiles -> G (n, B*K) fp16 (x 2^13)  [EpiG; never fp32, never S]
+//   dvideo  = G . T          (EpiStore, fp32 out)
+//   dtext   = G^T . V        bf16: G read as an MN-major UMMA operand, no transpose;
+//                            fp32: a transposed pass writes G^T planes first
+// The *_shard entry points are the rows-only multi-GPU variant: the column
+// statistic and dtext come out as per-rank partials for the caller to combine.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
