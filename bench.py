@@ -282,7 +282,7 @@ def run_b200(args):
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3},
-        "gpu_launches": 13 * (args.steps),
+        "gpu_launches": 8 * (args.steps),
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",

@@ -48,7 +48,8 @@ struct Scalars {
     float alpha_dtext;            // grad_loss / (B * 2^13 * s_video)
     float den_mid_log2;           // (min den + max den) / 2 in the log2 domain
     int g_fast;                   // 1: den range small enough for the one-exp gradient tile
-    int pad[7];
+    unsigned int ticket;          // blocks of merge_finalize_kernel that are done (last one reduces the loss)
+    int pad[6];
 };
 
 struct Plan {
@@ -61,8 +62,9 @@ struct Plan {
     long long ld_g2;         // G2 (B, n*K) for the sharded bf16 backward
     int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
     int nb_cl;               // 128-row blocks of the owned rows
+    int cg;                  // columns per column statistic: K when the epilogue pre-sums the K candidates, else 1
     int chunk_s, chunk_g;    // k-blocks per tensor-core accumulation chunk (S passes / grad GEMMs)
-    size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_g, off_gt, total;
+    size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_bsum, off_g, off_gt, total;
 };
 
 bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
@@ -81,7 +83,8 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.ld_g = p.ld_tt;
     p.ld_gt = p.ld_vt;
     // one row partial per epilogue warp column part; bf16 mode runs 256-wide pair tiles (all written)
-    p.nb_r = tc::EpiRowCol::PARTS * ((p.P == 1) ? 2 * (int)((p.BK + 255) / 256) : (int)((p.BK + BLOCK_N - 1) / BLOCK_N));
+    p.nb_r = tc::EpiRowCol::PARTS * ((p.P == 1) ? (int)((p.BK + 255) / 256) : (int)((p.BK + BLOCK_N - 1) / BLOCK_N));
+    p.cg = (p.P == 1 && (K == 2 || K == 4 || K == 8)) ? K : 1;
     // one column partial per 128-row block; bf16 mode runs 256-row tiles (both halves are written)
     p.nb_c = (p.P == 1) ? 2 * ((B + 255) / 256) : (B + 127) / 128;
     size_t o = 0;
@@ -93,8 +96,9 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.off_tt = take((size_t)D * p.ld_tt * 2);
     p.off_pr = take((size_t)p.nb_r * n * 4);
     p.nb_cl = 2 * ((n + 255) / 256);  // row blocks of the owned rows (rows-only sharding)
-    p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) * 4);
+    p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) / p.cg * 4);
     p.off_diff = take((size_t)n * 4 * 2);  // den - nom, then the merged den
+    p.off_bsum = take((size_t)((n + 31) / 32) * 8);  // per-block partial sums of den - nom (double)
     p.off_g = take((size_t)n * p.ld_g * 2);
     // P == 3: G^T (n*K, P*B) from the transposed pass.  P == 1: G2 = G[all rows, own columns]
     // (B, n*K), read MN-major by the dtext GEMM; not needed at all when n == B.
@@ -231,14 +235,34 @@ __global__ void stage_operand_kernel(const T *__restrict__ in, int rows, int D,
 }
 
 // bf16 fast path of the above (planes == 1, D % 8 == 0, 16-byte aligned rows): 64 x 64 tiles,
-// 16-byte global loads and stores on both the K-major copy and the transposed copy.
+// 16-byte global loads and stores on both the K-major copy and the transposed copy.  One launch
+// stages both tensors (blockIdx.y < tiles_v: video, else text) and derives the power-of-two
+// scales from the absmax bits itself; block (0, 0) publishes them for the later kernels.
+struct StageSide {
+    const __nv_bfloat16 *in;
+    int rows;
+    __half *outk;
+    long long ldk;
+    __half *outt;
+    long long ldt;
+};
 __global__ void __launch_bounds__(256)
-stage_bf16_kernel(const __nv_bfloat16 *__restrict__ in, int rows, int D,
-                  const float *__restrict__ scale_ptr, __half *__restrict__ outk, long long ldk,
-                  __half *__restrict__ outt, long long ldt) {
+stage_bf16_kernel(StageSide sv, StageSide stx, int tiles_v, int D, Scalars *scal) {
     __shared__ __half tile[64][64 + 2];  // +2 halves: conflict-free column reads
-    const float sc = *scale_ptr;
-    const int r0 = blockIdx.y * 64, d0 = blockIdx.x * 64;
+    const float s_v = pow2_scale(scal->absmax_bits[0]), s_t = pow2_scale(scal->absmax_bits[1]);
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {  // nobody reads these in this kernel
+        scal->s_video = s_v;
+        scal->s_text = s_t;
+        scal->inv_ss = (1.f / s_v) * (1.f / s_t);
+    }
+    const bool is_v = (int)blockIdx.x < tiles_v;  // row tiles on x (no 65535 limit), feature tiles on y
+    const __nv_bfloat16 *__restrict__ in = is_v ? sv.in : stx.in;
+    __half *__restrict__ outk = is_v ? sv.outk : stx.outk;
+    __half *__restrict__ outt = is_v ? sv.outt : stx.outt;
+    const int rows = is_v ? sv.rows : stx.rows;
+    const long long ldk = is_v ? sv.ldk : stx.ldk, ldt = is_v ? sv.ldt : stx.ldt;
+    const float sc = is_v ? s_v : s_t;
+    const int r0 = ((int)blockIdx.x - (is_v ? 0 : tiles_v)) * 64, d0 = blockIdx.y * 64;
     const int tid = threadIdx.x;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -278,9 +302,6 @@ stage_bf16_kernel(const __nv_bfloat16 *__restrict__ in, int rows, int D,
     }
 }
 
-// ----------------------------------------------------------------------------
-// finalize: one warp per owned sample
-// ----------------------------------------------------------------------------
 __device__ __forceinline__ float warp_max(float v) {
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
@@ -290,15 +311,108 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// bf16 fast path, first pass over the inputs (one launch instead of three): one warp per sample i
+// reads video[i] and its K candidates text[iK .. iK+K) once and produces
+//   - the running |x|max of both tensors (atomicMax on the float bits, like absmax_kernel)
+//   - nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs on the original values
+//     (loss.py:13-15), for the samples in [i0, i0+n) when nom != nullptr.
+// D % 8 == 0 and 16-byte aligned rows (checked by the caller).
+__global__ void __launch_bounds__(256)
+prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *__restrict__ text, int B,
+                 int K, int D, int i0, int n, float *__restrict__ nom, unsigned int *absmax_bits) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    float mv = 0.f, mt = 0.f;
+    auto amax8 = [](float m, const float (&f)[8]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float a = fabsf(f[j]);
+            if (a == a && a <= 3.0e38f) m = fmaxf(m, a);  // ignore NaN/inf for the scale choice
+        }
+        return m;
+    };
+    auto unpack8 = [](const uint4 &q, float (&f)[8]) {
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&q);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 v = __bfloat1622float2(h[j]);
+            f[2 * j] = v.x;
+            f[2 * j + 1] = v.y;
+        }
+    };
+    for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < B; i += gridDim.x * wpb) {
+        const bool want_nom = (nom != nullptr) && i >= i0 && i < i0 + n;
+        const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
+        float pm = -INFINITY, ps = 0.f;
+        for (int k = 0; k < K; ++k) {
+            const uint4 *trow = reinterpret_cast<const uint4 *>(text + ((size_t)i * K + k) * D);
+            float acc = 0.f;
+            for (int c = lane; c < D / 8; c += 32) {
+                float fv[8], ft[8];
+                unpack8(__ldg(vrow + c), fv);  // re-read per candidate: 1 KB per warp, stays in L1
+                unpack8(__ldg(trow + c), ft);
+                if (k == 0) mv = amax8(mv, fv);
+                mt = amax8(mt, ft);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc = fmaf(fv[j], ft[j], acc);
+            }
+            if (want_nom) {
+                acc = warp_sum(acc);
+                if (acc > pm) {
+                    ps = ps * expf(pm - acc) + 1.f;
+                    pm = acc;
+                } else {
+                    ps += expf(acc - pm);
+                }
+            }
+        }
+        if (want_nom && lane == 0) nom[i] = pm + logf(ps);
+    }
+    mv = warp_max(mv);
+    mt = warp_max(mt);
+    __shared__ float sv[8], stx[8];
+    if (lane == 0) {
+        sv[threadIdx.x >> 5] = mv;
+        stx[threadIdx.x >> 5] = mt;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < wpb; ++w) {
+            mv = fmaxf(mv, sv[w]);
+            mt = fmaxf(mt, stx[w]);
+        }
+        if (mv > 0.f) atomicMax(&absmax_bits[0], __float_as_uint(mv));
+        if (mt > 0.f) atomicMax(&absmax_bits[1], __float_as_uint(mt));
+    }
+}
+
+// ----------------------------------------------------------------------------
+// finalize: one warp per owned sample
+// ----------------------------------------------------------------------------
+
 // merge the per-tile partial log-sum-exps of 32 samples per block: lane = sample (coalesced
 // reads), the block's 32 warps stride over the partials, then combine through smem.
-//   part_r[t][w], t < nb_r          -> row_i = lse over all text columns
-//   part_c[t][w*K + k], t < nb_c    -> col_i = lse over all video rows and the K candidates
+//   part_r[t][w], t < nb_r           -> row_i = lse over all text columns
+//   part_c[t][w*kc + k], t < nb_c    -> col_i = lse over all video rows and the K candidates
+//                                       (kc = K / column-group statistics per sample)
+// out[w] = logaddexp(row_w, col_w).  With fin.den != nullptr the kernel also finishes the forward:
+// den, den - nom, and the loss (the last block to finish adds the per-block partial sums in a
+// fixed order, in double: deterministic).
+struct MergeFin {
+    const float *nom;   // indexed by global sample (i0 + w)
+    float *den;         // idem; nullptr: plain merge
+    float *diff;        // (n) den - nom
+    double *bsum;       // (gridDim.x) per-block sums of diff
+    unsigned int *ticket;
+    float *loss;
+    int i0, B;
+};
 __global__ void __launch_bounds__(1024)
-merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict__ part_c, int K, int n,
-                      int nb_r, int nb_c, float *__restrict__ rowcol) {
+merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict__ part_c, int kc, int n,
+                      int nb_r, int nb_c, float *__restrict__ out, MergeFin fin) {
     constexpr int NW = 32;
     __shared__ float sm[NW][32], ss[NW][32];
+    __shared__ bool is_last;
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     const int w = blockIdx.x * 32 + lane;
     float m = -INFINITY, s = 0.f;
@@ -312,29 +426,54 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     };
     if (w < n) {
         for (int t = wp; t < nb_r; t += NW) push(part_r[(size_t)t * n + w]);
-        const size_t nk = (size_t)n * K;
+        const size_t nk = (size_t)n * kc;
         for (int t = wp; t < nb_c; t += NW)
-            for (int k = 0; k < K; ++k) push(part_c[(size_t)t * nk + (size_t)w * K + k]);
+            for (int k = 0; k < kc; ++k) push(part_c[(size_t)t * nk + (size_t)w * kc + k]);
     }
     sm[wp][lane] = m;
     ss[wp][lane] = s;
     __syncthreads();
-    if (wp == 0 && w < n) {
+    if (wp != 0) return;
+    float d = 0.f;
+    if (w < n) {
         float mm = sm[0][lane];
         for (int j = 1; j < NW; ++j) mm = fmaxf(mm, sm[j][lane]);
         float tot = 0.f;
         for (int j = 0; j < NW; ++j)
             if (sm[j][lane] > -INFINITY) tot += ss[j][lane] * __expf(sm[j][lane] - mm);
-        rowcol[w] = mm + logf(tot);  // = logaddexp(row_i, col_i) = den_i  (loss.py:16-17)
+        const float dn = mm + logf(tot);  // = logaddexp(row_i, col_i) = den_i  (loss.py:16-17)
+        if (out != nullptr) out[w] = dn;
+        if (fin.den != nullptr) {
+            fin.den[fin.i0 + w] = dn;
+            d = dn - fin.nom[fin.i0 + w];
+            fin.diff[w] = d;
+        }
+    }
+    if (fin.den == nullptr) return;
+    double acc = (double)d;
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+        fin.bsum[blockIdx.x] = acc;
+        __threadfence();
+        is_last = (atomicAdd(fin.ticket, 1u) == gridDim.x - 1);
+    }
+    __syncwarp();
+    if (!is_last) return;
+    __threadfence();
+    acc = 0.0;
+    for (int b = lane; b < (int)gridDim.x; b += 32) acc += __ldcg(fin.bsum + b);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+        fin.loss[0] = (float)(acc / (double)fin.B);
+        *fin.ticket = 0;
     }
 }
 
-// warp per owned sample: positives from exact fp32 dot products (loss.py:13-15), den, den - nom
+// warp per owned sample: positives from exact fp32 dot products (loss.py:13-15); generic path
+// (the bf16 fast path gets them from prep_bf16_kernel)
 template <typename T>
-__global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict__ text,
-                                const float *__restrict__ rowcol, int K, int D, int i0, int n,
-                                float *__restrict__ den, float *__restrict__ nom,
-                                float *__restrict__ diff) {
+__global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict__ text, int K, int D,
+                                int i0, int n, float *__restrict__ nom) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (w >= n) return;
@@ -353,30 +492,7 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
             ps += expf(acc - pm);
         }
     }
-    if (lane == 0) {
-        const float nm = pm + logf(ps);
-        nom[i] = nm;
-        if (rowcol != nullptr) {  // (null: rows-only sharding, den is formed after the exchange)
-            const float dn = rowcol[w];
-            den[i] = dn;
-            diff[w] = dn - nm;
-        }
-    }
-}
-
-// deterministic single-block reduction: loss = sum(diff) / B, accumulated in double
-__global__ void loss_reduce_kernel(const float *__restrict__ diff, int n, int B, float *loss) {
-    __shared__ double sh[32];
-    double acc = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += (double)diff[i];
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        acc = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (threadIdx.x == 0) loss[0] = (float)(acc / (double)B);
-    }
+    if (lane == 0) nom[i] = pm + logf(ps);
 }
 
 // ----------------------------------------------------------------------------
@@ -417,20 +533,10 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     return 0;
 }
 
-// bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.  B200HEAD_GEMM=1cta in the
-// environment selects the one-CTA 256 x 128 kernel instead (for A/B measurements).
-bool use_2cta() {
-    static const bool v = [] {
-        const char *e = getenv("B200HEAD_GEMM");
-        return !(e && strcmp(e, "1cta") == 0);
-    }();
-    return v;
-}
-
+// bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.
 template <class Epi, bool A_MN = false, bool N_FAST = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                  const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
-    if (!use_2cta()) return launch_gemm<Epi, A_MN, 2, N_FAST>(A, lda, Bm, ldb, M, N, Kd, 0, ep, stream, what);
     using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
     CUtensorMap ma, mb;
     int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
@@ -450,35 +556,46 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     return 0;
 }
 
+// Stages video/text into the fp16 operands.  When `nom` is non-null the positives' log-sum-exp of
+// the owned samples is produced on the way (bf16 fast path) or by finalize_kernel (generic path).
 template <typename T>
-int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cudaStream_t st) {
+int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cudaStream_t st, float *nom) {
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     B200_CUDA_OK(cudaMemsetAsync(sc, 0, sizeof(Scalars), st));
-    const size_t cv = (size_t)p.B * p.D, ct = (size_t)p.BK * p.D;
-    absmax_kernel<T><<<(unsigned)std::min<size_t>((cv + 1023) / 1024, 1184), 256, 0, st>>>(
-        video, cv, &sc->absmax_bits[0]);
-    absmax_kernel<T><<<(unsigned)std::min<size_t>((ct + 1023) / 1024, 1184), 256, 0, st>>>(
-        text, ct, &sc->absmax_bits[1]);
-    scalars_forward_kernel<<<1, 1, 0, st>>>(sc);
     __half *vk_ = reinterpret_cast<__half *>(ws + p.off_vk), *vt_ = reinterpret_cast<__half *>(ws + p.off_vt);
     __half *tk_ = reinterpret_cast<__half *>(ws + p.off_tk), *tt_ = reinterpret_cast<__half *>(ws + p.off_tt);
     bool fast = false;
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
         fast = (p.D % 8 == 0) && (((uintptr_t)video & 15) == 0) && (((uintptr_t)text & 15) == 0);
         if (fast) {
-            dim3 gv((p.D + 63) / 64, (p.B + 63) / 64), gt((p.D + 63) / 64, (unsigned)((p.BK + 63) / 64));
-            stage_bf16_kernel<<<gv, 256, 0, st>>>(video, p.B, p.D, &sc->s_video, vk_, p.ld_vk, vt_, p.ld_vt);
-            stage_bf16_kernel<<<gt, 256, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, tk_, p.ld_tk, tt_,
-                                                  p.ld_tt);
+            const int wpb = 8;
+            const int blocks = std::min((p.B + wpb - 1) / wpb, 8 * num_sms());
+            prep_bf16_kernel<<<blocks, wpb * 32, 0, st>>>(video, text, p.B, p.K, p.D, p.i0, p.n, nom,
+                                                          sc->absmax_bits);
+            const int tiles_v = (p.B + 63) / 64, tiles_t = (int)((p.BK + 63) / 64);
+            StageSide sv{video, p.B, vk_, p.ld_vk, vt_, p.ld_vt};
+            StageSide stx{text, (int)p.BK, tk_, p.ld_tk, tt_, p.ld_tt};
+            stage_bf16_kernel<<<dim3(tiles_v + tiles_t, (p.D + 63) / 64), 256, 0, st>>>(sv, stx, tiles_v, p.D, sc);
         }
     }
     if (!fast) {
+        const size_t cv = (size_t)p.B * p.D, ct = (size_t)p.BK * p.D;
+        absmax_kernel<T><<<(unsigned)std::min<size_t>((cv + 1023) / 1024, 1184), 256, 0, st>>>(
+            video, cv, &sc->absmax_bits[0]);
+        absmax_kernel<T><<<(unsigned)std::min<size_t>((ct + 1023) / 1024, 1184), 256, 0, st>>>(
+            text, ct, &sc->absmax_bits[1]);
+        scalars_forward_kernel<<<1, 1, 0, st>>>(sc);
         dim3 blk(32, 8);
         dim3 gv((p.D + 31) / 32, (p.B + 31) / 32), gt((p.D + 31) / 32, (unsigned)((p.BK + 31) / 32));
         stage_operand_kernel<T><<<gv, blk, 0, st>>>(video, p.B, p.D, &sc->s_video, p.P, true, vk_, p.ld_vk,
                                                     vt_, p.ld_vt);
         stage_operand_kernel<T><<<gt, blk, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, p.P, false, tk_,
                                                     p.ld_tk, tt_, p.ld_tt);
+        if (nom != nullptr) {
+            const int warps_per_block = 8;
+            finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
+                video, text, p.K, p.D, p.i0, p.n, nom);
+        }
     }
     B200_LAUNCH_OK("staging kernels");
     return 0;
@@ -500,10 +617,28 @@ int check_common(const Plan &p, const void *ws, size_t ws_bytes) {
     return 0;
 }
 
+// statistics GEMM with the column-group size chosen at run time (Plan::cg)
+template <int G>
+int launch_stats2_g(const float *scale, float *pr, long long ldr, float *pc, long long ldc, const void *A,
+                    long long lda, const void *Bm, long long ldb, int M, int N, int Kd, cudaStream_t st,
+                    const char *what) {
+    typename tc::EpiRowColT<G>::Params e{pr, ldr, pc, ldc, scale};
+    return launch_gemm2<tc::EpiRowColT<G>>(A, lda, Bm, ldb, M, N, Kd, e, st, what);
+}
+template <class... Args>
+int launch_stats2(int cg, Args... a) {
+    switch (cg) {
+        case 2: return launch_stats2_g<2>(a...);
+        case 4: return launch_stats2_g<4>(a...);
+        case 8: return launch_stats2_g<8>(a...);
+        default: return launch_stats2_g<1>(a...);
+    }
+}
+
 template <typename T>
 int forward_impl(const Plan &p, const T *video, const T *text, float *den, float *nom, float *loss,
                  uint8_t *ws, cudaStream_t st) {
-    int rc = stage_inputs<T>(p, video, text, ws, st);
+    int rc = stage_inputs<T>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
@@ -512,38 +647,43 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
     float *diff = reinterpret_cast<float *>(ws + p.off_diff);
     const int Kd = p.P * p.D;
-    float *rowcol = diff + p.n;
+    const long long ldc = (long long)p.n * p.K / p.cg;  // column statistics of the owned samples
     if (p.n == p.B) {
         // one pass over S: row statistic per thread, column statistic by a cross-lane reduction
-        tc::EpiRowCol::Params e{pr, (long long)p.n, pc, (long long)p.BK, &sc->inv_ss};
         const char *what = "milnce forward (fused row+column statistics)";
-        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd, e, st, what)
-                        : launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd,
-                                                     p.chunk_s, e, st, what);
+        if (p.P == 1) {
+            rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, pc, ldc, vk, p.ld_vk, tk, p.ld_tk, p.B,
+                               (int)p.BK, Kd, st, what);
+        } else {
+            tc::EpiRowCol::Params e{pr, (long long)p.n, pc, ldc, &sc->inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd, p.chunk_s, e, st, what);
+        }
         if (rc) return rc;
     } else {
         // sharded: rows [i0, i0+n) x all columns -> row statistic of the owned samples
-        tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, &sc->inv_ss};
         const __half *va = vk + (size_t)p.i0 * p.ld_vk;
-        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, er, st,
-                                                     "milnce forward row block")
-                        : launch_gemm<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd,
-                                                     p.chunk_s, er, st, "milnce forward row block");
-        if (rc) return rc;
         // all rows x columns of the owned samples -> their column statistic
-        tc::EpiRowCol::Params ec{nullptr, 0, pc, (long long)p.n * p.K, &sc->inv_ss};
         const __half *tb = tk + (size_t)p.i0 * p.K * p.ld_tk;
-        rc = (p.P == 1) ? launch_gemm2<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd, ec, st,
-                                                     "milnce forward column block")
-                        : launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd,
-                                                     p.chunk_s, ec, st, "milnce forward column block");
+        if (p.P == 1) {
+            rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, nullptr, 0, va, p.ld_vk, tk, p.ld_tk, p.n,
+                               (int)p.BK, Kd, st, "milnce forward row block");
+            if (rc) return rc;
+            rc = launch_stats2(p.cg, &sc->inv_ss, nullptr, 0, pc, ldc, vk, p.ld_vk, tb, p.ld_tk, p.B,
+                               p.n * p.K, Kd, st, "milnce forward column block");
+        } else {
+            tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, &sc->inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, er, st,
+                                            "milnce forward row block");
+            if (rc) return rc;
+            tc::EpiRowCol::Params ec{nullptr, 0, pc, ldc, &sc->inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd, p.chunk_s, ec, st,
+                                            "milnce forward column block");
+        }
         if (rc) return rc;
     }
-    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, pc, p.K, p.n, p.nb_r, p.nb_c, rowcol);
-    const int warps_per_block = 8;
-    finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
-        video, text, rowcol, p.K, p.D, p.i0, p.n, den, nom, diff);
-    loss_reduce_kernel<<<1, 1024, 0, st>>>(diff, p.n, p.B, loss);
+    MergeFin fin{nom, den, diff, reinterpret_cast<double *>(ws + p.off_bsum), &sc->ticket, loss, p.i0, p.B};
+    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, pc, p.K / p.cg, p.n, p.nb_r, p.nb_c, nullptr,
+                                                            fin);
     B200_LAUNCH_OK("milnce finalize");
     return 0;
 }
@@ -554,7 +694,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                   cudaStream_t st) {
     int rc;
     if (!reuse) {
-        rc = stage_inputs<T>(p, video, text, ws, st);
+        rc = stage_inputs<T>(p, video, text, ws, st, nullptr);
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
@@ -568,7 +708,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     const int Kd = p.P * p.D;
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     // row block: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
-    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, 1, 0, p.K, &sc->inv_ss, fast};
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
     const __half *va = vk + (size_t)p.i0 * p.ld_vk;
     rc = (p.P == 1) ? launch_gemm2<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, gr, st,
                                            "milnce backward row block")
@@ -593,7 +733,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         long long ld_g2 = p.ld_g;
         if (p.n != p.B) {
             // column block: G2 (B, n*K): row <-> sample r, column c <-> sample (i0*K + c) / K
-            tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, 1, p.i0 * p.K, p.K,
+            tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, tc::make_fastdiv(1), p.i0 * p.K, tc::make_fastdiv(p.K),
                                 &sc->inv_ss, fast};
             rc = launch_gemm2<tc::EpiG>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
                                         p.n * p.K, Kd, gc, st, "milnce backward column block");
@@ -606,7 +746,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         return rc;
     }
     // fp32 inputs (hi/lo planes): the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
-    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, p.K, 0, 1, &sc->inv_ss,
+    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, tc::make_fastdiv(p.K), 0, tc::make_fastdiv(1), &sc->inv_ss,
                         fast};
     rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
                                p.B, Kd, p.chunk_s, gc, st, "milnce backward transposed block");
@@ -627,24 +767,21 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
 // ---------------------------------------------------------------------------------------------
 int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
                        float *row_lse, float *col_part, float *nom, uint8_t *ws, cudaStream_t st) {
-    int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st);
+    int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
-    tc::EpiRowCol::Params e{pr, (long long)p.n, pc, (long long)p.BK, &sc->inv_ss};
-    rc = launch_gemm2<tc::EpiRowCol>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK,
-                                     p.D, e, st, "milnce forward (rows-only shard)");
+    rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * p.ld_vk,
+                       p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
     if (rc) return rc;
-    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, p.K, p.n, p.nb_r, 0,
-                                                            row_lse + p.i0);
-    merge_partials_kernel<<<(p.B + 31) / 32, 1024, 0, st>>>(nullptr, pc, p.K, p.B, 0, p.nb_cl, col_part);
-    const int warps_per_block = 8;
-    finalize_kernel<__nv_bfloat16><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32,
-                                     0, st>>>(video, text, nullptr, p.K, p.D, p.i0, p.n, nullptr, nom,
-                                              nullptr);
+    const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, 1, p.n, p.nb_r, 0, row_lse + p.i0,
+                                                            none);
+    merge_partials_kernel<<<(p.B + 31) / 32, 1024, 0, st>>>(nullptr, pc, p.K / p.cg, p.B, 0, p.nb_cl, col_part,
+                                                            none);
     B200_LAUNCH_OK("milnce shard finalize");
     return 0;
 }
@@ -654,7 +791,7 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
                         float *dtext_partial, int reuse, uint8_t *ws, cudaStream_t st) {
     int rc;
     if (!reuse) {
-        rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st);
+        rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
@@ -665,7 +802,7 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
-    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, 1, 0, p.K, &sc->inv_ss, fast};
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
     rc = launch_gemm2<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
                                 st, "milnce backward (rows-only shard) G");
     if (rc) return rc;

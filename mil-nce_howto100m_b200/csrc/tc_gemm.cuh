@@ -191,6 +191,55 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
+// Division of a non-negative 32-bit integer by a runtime constant without the ~20-instruction
+// software divide (the epilogues divide row/column indices by K several times per 32 columns).
+// Granlund-Montgomery round-up form, exact for every 32-bit numerator and d >= 1.
+struct FastDiv {
+    uint32_t mul, sh1, sh2;
+    int d;
+    __device__ __forceinline__ int div(int n) const {
+        const uint32_t t = __umulhi(mul, (uint32_t)n);
+        return (int)((t + (((uint32_t)n - t) >> sh1)) >> sh2);
+    }
+};
+inline FastDiv make_fastdiv(int d) {
+    uint32_t l = 0;
+    while ((1ull << l) < (unsigned long long)d) ++l;
+    FastDiv f;
+    f.d = d;
+    f.mul = (uint32_t)((((1ull << l) - (unsigned long long)d) << 32) / (unsigned long long)d + 1ull);
+    f.sh1 = l < 1 ? l : 1;
+    f.sh2 = l > 0 ? l - 1 : 0;
+    return f;
+}
+
+// explicit shared-space accesses: pointers that travel through EpiCtx are generic to the
+// compiler, which then emits generic LD/ST for them
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4 &v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z),
+                 "r"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(addr)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32f(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 lds128f(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(addr)
+                 : "memory");
+    return v;
+}
+
 // ----------------------------------------------------------------------------
 // Epilogue context handed to the functors
 // ----------------------------------------------------------------------------
@@ -213,6 +262,7 @@ struct EpiCtx {
     float *scratch;    // SCRATCH_FLOATS floats of smem shared by the epilogue warps
     uint8_t *stage;    // Epi::STAGE_BYTES bytes of smem (this warp's slice starts at warp_slot)
     int warp_slot;     // 0 .. 4*PARTS-1
+    int sub, nsub;     // column sub-block of the tile this run covers, and how many a tile has (1 or 2)
 };
 constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 // Every functor receives the finished fp32 accumulator (its row, its column half) in
@@ -229,10 +279,18 @@ struct EpiStore {
         float alpha;
         const float *alpha_dev;  // optional device scalar multiplied into alpha
     };
+    struct Tile {
+        float alpha;
+    };
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &) {
+        Tile t;
+        t.alpha = p.alpha;
+        if (p.alpha_dev) t.alpha *= __ldg(p.alpha_dev);
+        return t;
+    }
     template <int HN>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
-        float alpha = p.alpha;
-        if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
+    __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
+        const float alpha = t.alpha;
         const int row = c.m0 + c.tid;
         if (row >= c.M) return;
 #pragma unroll
@@ -266,8 +324,8 @@ struct EpiStore {
 // A row or column whose sum underflows under the shared shift (everything in it more than
 // 2^100 below wmax) is recomputed exactly with its own maximum - rare, so the common case
 // pays nothing for arbitrary logit ranges (embeddings are not normalised).
-template <int H>
-__device__ __forceinline__ void bfly_step(float (&a)[32], int lane) {
+template <int H, int N>
+__device__ __forceinline__ void bfly_step(float (&a)[N], int lane) {
     const bool up = (lane & H) != 0;
 #pragma unroll
     for (int j = 0; j < H; ++j) {
@@ -275,6 +333,21 @@ __device__ __forceinline__ void bfly_step(float (&a)[32], int lane) {
         const float keep = up ? a[j + H] : a[j];
         a[j] = keep + __shfl_xor_sync(0xffffffffu, send, H);
     }
+}
+// a[0..N) per lane, N a power of two <= 32: on return a[0] of lane l holds the sum over all 32
+// lanes of the original a[l % N] (transposing butterfly, then plain xor-sums over the lanes that
+// share l % N).  N - 1 + log2(32 / N) shuffles.
+template <int N>
+__device__ __forceinline__ float warp_transpose_sum(float (&a)[N], int lane) {
+    if constexpr (N >= 32) bfly_step<16, N>(a, lane);
+    if constexpr (N >= 16) bfly_step<8, N>(a, lane);
+    if constexpr (N >= 8) bfly_step<4, N>(a, lane);
+    if constexpr (N >= 4) bfly_step<2, N>(a, lane);
+    if constexpr (N >= 2) bfly_step<1, N>(a, lane);
+    float v = a[0];
+#pragma unroll
+    for (int o = N; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
 }
 __device__ __forceinline__ float warp_max_f(float v) {
 #pragma unroll
@@ -288,9 +361,18 @@ __device__ __forceinline__ float warp_sum_f(float v) {
 }
 constexpr float TINY_SUM = 7.8886090522101181e-31f;  // 2^-100
 
-struct EpiRowCol {
+// G = column group: the column statistic is wanted per group of G adjacent columns (the K
+// candidates of one sample, loss.py:16, when K is a power of two <= 32), so the G exponentials
+// are added inside the thread before the cross-lane reduction: 32/G - 1 + log2(G) shuffles per 32
+// columns instead of 31.  G = 1 keeps one statistic per column (any K).
+//   part_row[PARTS*(n_blk/nsub) + part][row] = log sum_{n in part of the tile} exp(s[row, n])
+//   part_col[m_blk][col / G]                 = log sum_{m in tile, n in group} exp(s[m, n])
+template <int G>
+struct EpiRowColT {
+    static_assert(G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32, "group size");
     static constexpr int STAGE_BYTES = 0;
     static constexpr int PARTS = 2;
+    static constexpr int NG = 32 / G;  // statistics per 32 columns
     struct Params {
         float *part_row;  // may be null: skip the row statistic
         long long ldr;
@@ -298,10 +380,20 @@ struct EpiRowCol {
         long long ldc;
         const float *scale_dev;
     };
+    struct Tile {
+        float sc;
+        float row_run;  // row statistic carried across the column sub-blocks of one tile (log2)
+    };
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &) {
+        Tile t;
+        t.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        t.row_run = -INFINITY;
+        return t;
+    }
     template <int HN>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
+    __device__ static void run(const Params &p, const EpiCtx &c, Tile &t, float (&acc)[HN]) {
         static_assert(HN * PARTS == 128, "scratch layout assumes 128-wide column blocks");
-        const float sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        const float sc = t.sc;
         const int lane = c.lane;
         const int row = c.m0 + c.tid;
         const bool row_ok = row < c.M;
@@ -322,31 +414,42 @@ struct EpiRowCol {
             float rs = 0.f;
 #pragma unroll
             for (int ch = 0; ch < HN / 32; ++ch) {
-                float a[32];
+                float g[NG];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    a[j] = row_ok ? fast_exp2(fmaf(acc[ch * 32 + j], sc, -wmax)) : 0.f;
-                    rs += a[j];
+                for (int u = 0; u < NG; ++u) {
+                    float gs = 0.f;
+#pragma unroll
+                    for (int v = 0; v < G; ++v)
+                        gs += row_ok ? fast_exp2(fmaf(acc[ch * 32 + u * G + v], sc, -wmax)) : 0.f;
+                    g[u] = gs;
+                    rs += gs;
                 }
                 wl[ch] = -INFINITY;
                 if (want_col) {
-                    bfly_step<16>(a, lane);
-                    bfly_step<8>(a, lane);
-                    bfly_step<4>(a, lane);
-                    bfly_step<2>(a, lane);
-                    bfly_step<1>(a, lane);
-                    const float cs = a[0];
+                    const float cs = warp_transpose_sum<NG>(g, lane);  // lane l: group l % NG
                     wl[ch] = wmax + log2f(cs);
-                    const bool valid_col = (c.n0 + ch * 32 + lane) < c.N;
-                    if (__any_sync(0xffffffffu, valid_col && cs < TINY_SUM)) {
-                        // exact per-column path for this 32x32 block
+                    const bool valid = (c.n0 + ch * 32 + (lane % NG) * G) < c.N;
+                    if (__any_sync(0xffffffffu, valid && cs < TINY_SUM)) {
+                        // exact path for this 32 x 32 block: every column with its own maximum,
+                        // the G columns of a group merged on the fly (uniform across lanes)
+                        float gm = -INFINITY, gsum = 0.f;
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const float y = row_ok ? acc[ch * 32 + j] * sc : -INFINITY;
                             const float cm = warp_max_f(y);
                             const float e = (cm > -INFINITY) ? fast_exp2(y - cm) : 0.f;
                             const float s = warp_sum_f(e);
-                            if (lane == j) wl[ch] = cm + log2f(s);
+                            if (cm > gm) {
+                                gsum = gsum * fast_exp2(gm - cm) + s;  // gm = -inf: 2^-inf = 0
+                                gm = cm;
+                            } else if (cm > -INFINITY) {
+                                gsum += s * fast_exp2(cm - gm);
+                            }
+                            if ((j % G) == G - 1) {
+                                if ((lane % NG) == j / G) wl[ch] = (gm > -INFINITY) ? gm + log2f(gsum) : -INFINITY;
+                                gm = -INFINITY;
+                                gsum = 0.f;
+                            }
                         }
                     }
                 }
@@ -362,16 +465,28 @@ struct EpiRowCol {
 #pragma unroll
             for (int ch = 0; ch < HN / 32; ++ch) wl[ch] = -INFINITY;
         }
-        if (p.part_row != nullptr && row_ok)
-            p.part_row[(long long)(c.n_blk * PARTS + c.half) * p.ldr + row] = row_lse * LN2;
+        if (p.part_row != nullptr) {
+            // one row partial per (tile, column part): merge the tile's column sub-blocks first
+            float acc_lse = row_lse;
+            if (c.sub > 0) {
+                const float m = fmaxf(t.row_run, row_lse);
+                acc_lse = (m > -INFINITY) ? m + log2f(fast_exp2(t.row_run - m) + fast_exp2(row_lse - m)) : m;
+            }
+            t.row_run = acc_lse;
+            if (c.sub == c.nsub - 1 && row_ok)
+                p.part_row[(long long)((c.n_blk >> (c.nsub - 1)) * PARTS + c.half) * p.ldr + row] = acc_lse * LN2;
+        }
         if (want_col) {
             // merge the four lane-quarters' partials through smem (double-buffered by tile parity)
+            constexpr int NGB = 128 / G;  // statistics per 128-column block
             float *buf = c.scratch + c.par * (4 * 128);
+            if (lane < NG) {
 #pragma unroll
-            for (int ch = 0; ch < HN / 32; ++ch)
-                buf[c.q * 128 + c.half * HN + ch * 32 + lane] = wl[ch];
+                for (int ch = 0; ch < HN / 32; ++ch)
+                    buf[c.q * 128 + (c.half * HN + ch * 32) / G + lane] = wl[ch];
+            }
             epi_bar_sync(c.nthreads);
-            if (c.etid < 128) {
+            if (c.etid < NGB) {
                 const float v0 = buf[c.etid], v1 = buf[128 + c.etid], v2 = buf[256 + c.etid],
                             v3 = buf[384 + c.etid];
                 const float m = fmaxf(fmaxf(v0, v1), fmaxf(v2, v3));
@@ -379,12 +494,13 @@ struct EpiRowCol {
                 if (m > -INFINITY)
                     out = (m + log2f(fast_exp2(v0 - m) + fast_exp2(v1 - m) + fast_exp2(v2 - m) +
                                      fast_exp2(v3 - m))) * LN2;
-                const int col = c.n_blk * 128 + c.etid;
-                if (col < c.N) p.part_col[(long long)c.m_blk * p.ldc + col] = out;
+                if (c.n_blk * 128 + c.etid * G < c.N)
+                    p.part_col[(long long)c.m_blk * p.ldc + c.n_blk * NGB + c.etid] = out;
             }
         }
     }
 };
+using EpiRowCol = EpiRowColT<1>;
 
 // ---- softmax-gradient tile (MIL-NCE backward; autograd of loss.py:11-18) ----
 // G[r, n] = 2^13 * ( e^{s - den[rs]} + e^{s - den[cs]} - [rs == cs] e^{s - nom[rs]} ),
@@ -412,13 +528,16 @@ struct EpiG {
         long long ldo;
         long long plane_stride;  // = N (columns per plane)
         int planes;              // 1 or 3
-        int row_off, rdiv, col_off, cdiv;
+        int row_off;
+        FastDiv rdiv;
+        int col_off;
+        FastDiv cdiv;
         const float *scale_dev;
         GFast fast;
     };
     // write this warp's 32 x HN fp16 sub-tile (already scaled, packed) to one plane of `out`
     template <int HN>
-    __device__ static void store_plane(const EpiCtx &c, uint8_t *wstage, const uint32_t (&packed)[HN / 2],
+    __device__ static void store_plane(const EpiCtx &c, uint32_t wstage, const uint32_t (&packed)[HN / 2],
                                        __half *out, long long ldo) {
         constexpr int CH = HN / 8;        // 16-byte chunks per row (8 or 4)
         constexpr int ROWB = HN * 2;      // bytes per staged row (128 or 64)
@@ -428,87 +547,127 @@ struct EpiG {
         const int r = c.lane;
         const int rot = (CH == 8) ? (r & 7) : ((r >> 1) & 3);
 #pragma unroll
-        for (int k = 0; k < CH; ++k) {
-            uint4 v = make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]);
-            *reinterpret_cast<uint4 *>(wstage + r * ROWB + ((k ^ rot) << 4)) = v;
-        }
+        for (int k = 0; k < CH; ++k)
+            sts128(wstage + r * ROWB + ((k ^ rot) << 4),
+                   make_uint4(packed[4 * k], packed[4 * k + 1], packed[4 * k + 2], packed[4 * k + 3]));
         __syncwarp();
         // write-out: lane -> (row = it*RPI + lane/CH, chunk = lane%CH): full 16-byte chunks, RPI rows
         const int sub = c.lane / CH, k = c.lane % CH;
         const int col = c.n0 + k * 8;
+        const int row0 = c.m0 + c.q * 32;
+        __half *dst0 = out + (long long)(row0 + sub) * ldo + col;
+        // interior sub-tile with 16-byte aligned rows (warp-uniform): no per-chunk checks
+        const bool interior = (row0 + 32 <= c.M) && (c.n0 + HN <= c.N) && ((ldo & 7) == 0) &&
+                              ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+        if (interior) {
+            const long long step = (long long)RPI * ldo;
 #pragma unroll
-        for (int it = 0; it < CH; ++it) {
-            const int rr = it * RPI + sub;
-            const int grow = c.m0 + c.q * 32 + rr;
-            const int rrot = (CH == 8) ? (rr & 7) : ((rr >> 1) & 3);
-            const uint4 v = *reinterpret_cast<const uint4 *>(wstage + rr * ROWB + ((k ^ rrot) << 4));
-            if (grow < c.M) {
-                __half *dst = out + (long long)grow * ldo + col;
-                if (col + 8 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
-                    *reinterpret_cast<uint4 *>(dst) = v;
-                } else {
-                    const __half *hv = reinterpret_cast<const __half *>(&v);
-#pragma unroll
-                    for (int e = 0; e < 8; ++e)
-                        if (col + e < c.N) dst[e] = hv[e];
+            for (int it = 0; it < CH; ++it) {
+                const int rr = it * RPI + sub;
+                const int rrot = (CH == 8) ? (rr & 7) : ((rr >> 1) & 3);
+                *reinterpret_cast<uint4 *>(dst0 + it * step) = lds128(wstage + rr * ROWB + ((k ^ rrot) << 4));
+            }
+        } else {
+#pragma unroll 1
+            for (int it = 0; it < CH; ++it) {
+                const int rr = it * RPI + sub;
+                const int grow = row0 + rr;
+                const int rrot = (CH == 8) ? (rr & 7) : ((rr >> 1) & 3);
+                const uint4 v = lds128(wstage + rr * ROWB + ((k ^ rrot) << 4));
+                if (grow < c.M) {
+                    __half *dst = out + (long long)grow * ldo + col;
+                    if (col + 8 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
+                        *reinterpret_cast<uint4 *>(dst) = v;
+                    } else {
+                        const __half *hv = reinterpret_cast<const __half *>(&v);
+                        for (int e = 0; e < 8; ++e)
+                            if (col + e < c.N) dst[e] = hv[e];
+                    }
                 }
             }
         }
         __syncwarp();
     }
+    // per-tile state: everything that depends only on the row block (c.m0, c.tid), loaded once per
+    // tile instead of once per 32-column run.  Kept to what the common path needs (the kernel
+    // runs at 96 registers per thread); the rare paths re-derive the rest.
+    struct Tile {
+        bool fast;
+        float mid, sc, dr13, ar;
+        int n_lo, n_hi;  // columns whose sample is one of this row block's samples: [n_lo, n_hi)
+    };
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c) {
+        Tile t;
+        t.fast = __ldg(p.fast.flag_dev) != 0;
+        t.mid = __ldg(p.fast.mid_log2_dev);
+        t.sc = __ldg(p.scale_dev) * LOG2E;
+        const int row = c.m0 + c.tid;
+        const int rs = p.rdiv.div(p.row_off + min(row, c.M - 1));
+        const float dr = __ldg(p.den + rs) * LOG2E;
+        t.dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
+        t.ar = t.fast ? fast_exp2(dr - t.mid) : 0.f;
+        const int rs_lo = p.rdiv.div(p.row_off + c.m0);
+        const int rs_hi = p.rdiv.div(p.row_off + min(c.m0 + BLOCK_M, c.M) - 1);
+        t.n_lo = rs_lo * p.cdiv.d - p.col_off;
+        t.n_hi = (rs_hi + 1) * p.cdiv.d - p.col_off;
+        return t;
+    }
     template <int HN>
-    __device__ static void run(const Params &p, const EpiCtx &c, float (&acc)[HN]) {
+    __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
         static_assert(HN == 64 || HN == 32, "staging layout: 64 or 32 columns per warp");
-        const bool fast = __ldg(p.fast.flag_dev) != 0;
-        const float mid = __ldg(p.fast.mid_log2_dev);
+        const bool fast = t.fast;
+        const float mid = t.mid;
         // per-column factors of this warp's 64 columns, in the warp's own 256 bytes of smem:
         // no CTA-wide barrier (a shared table made all eight warps wait for the slowest den load)
-        float *tab = c.scratch + c.warp_slot * HN;
+        const uint32_t tab = smem_u32(c.scratch) + (uint32_t)(c.warp_slot * HN * 4);
 #pragma unroll
         for (int h = 0; h < HN / 32; ++h) {
             const int n = c.n0 + h * 32 + c.lane;
             float t;
             if (n < c.N) {
-                const float dc = __ldg(p.den + (p.col_off + n) / p.cdiv) * LOG2E;
+                const float dc = __ldg(p.den + p.cdiv.div(p.col_off + n)) * LOG2E;
                 t = fast ? fast_exp2(mid - dc) : dc;  // fast: column factor 2^(mid - den_c)
             } else {
                 t = fast ? 0.f : INFINITY;  // masked column (never stored)
             }
-            tab[h * 32 + c.lane] = t;
+            sts32f(tab + (uint32_t)((h * 32 + c.lane) * 4), t);
         }
         __syncwarp();
-        const float sc = __ldg(p.scale_dev) * LOG2E;
-        const int row = c.m0 + c.tid;
-        const int rs = (p.row_off + min(row, c.M - 1)) / p.rdiv;
-        const float dr = __ldg(p.den + rs) * LOG2E;
-        const float nr = __ldg(p.nom + rs) * LOG2E;
-        const float dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
-        const float ar = fast ? fast_exp2(dr - mid) : 0.f;
-        // does this half tile touch the positives (row sample == column sample)?
-        const int rs_lo = (p.row_off + c.m0) / p.rdiv;
-        const int rs_hi = (p.row_off + min(c.m0 + BLOCK_M, c.M) - 1) / p.rdiv;
-        const int cs_lo = (p.col_off + c.n0) / p.cdiv;
-        const int cs_hi = (p.col_off + min(c.n0 + HN, c.N) - 1) / p.cdiv;
-        const bool diag_tile = (c.n0 < c.N) && !(rs_hi < cs_lo || cs_hi < rs_lo);
+        const float sc = t.sc, dr13 = t.dr13, ar = t.ar;
+        // does this run touch the positives (row sample == column sample)?
+        const bool diag_tile = (c.n0 < c.N) && (c.n0 < t.n_hi) && (c.n0 + HN > t.n_lo);
         if (!diag_tile) {
             if (fast) {
 #pragma unroll
-                for (int i = 0; i < HN; ++i) {
-                    const float e = fast_exp2(fmaf(acc[i], sc, -dr13));
-                    acc[i] = fmaf(e, ar * tab[i], e);
+                for (int i = 0; i < HN; i += 4) {
+                    const float4 t4 = lds128f(tab + (uint32_t)(i * 4));
+                    const float tv[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float e = fast_exp2(fmaf(acc[i + u], sc, -dr13));
+                        acc[i + u] = fmaf(e, ar * tv[u], e);
+                    }
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < HN; ++i) {
-                    const float y = acc[i] * sc;
-                    acc[i] = (fast_exp2(y - dr) + fast_exp2(y - tab[i])) * G_SCALE;
+                for (int i = 0; i < HN; i += 4) {
+                    const float4 t4 = lds128f(tab + (uint32_t)(i * 4));
+                    const float tv[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float y = acc[i + u] * sc;
+                        acc[i + u] = (fast_exp2(y - dr13) + fast_exp2(y - tv[u] + 13.f));
+                    }
                 }
             }
         } else {
+            const int rs = p.rdiv.div(p.row_off + min(c.m0 + c.tid, c.M - 1));
+            const float dr = dr13 + 13.f;
+            const float nr = __ldg(p.nom + rs) * LOG2E;
 #pragma unroll
             for (int i = 0; i < HN; ++i) {
                 const float y = acc[i] * sc;
-                const int cs = (p.col_off + c.n0 + i) / p.cdiv;
+                const int cs = p.cdiv.div(p.col_off + c.n0 + i);
                 const float dc = (c.n0 + i < c.N) ? __ldg(p.den + cs) * LOG2E : INFINITY;
                 float g = fast_exp2(y - dr) + fast_exp2(y - dc);
                 if (cs == rs) g -= fast_exp2(y - nr);  // the positives
@@ -517,7 +676,7 @@ struct EpiG {
         }
         __syncwarp();             // all lanes are done with this run's table
         if (c.n0 >= c.N) return;  // warp-uniform: nothing of this half is inside the matrix
-        uint8_t *wstage = c.stage + c.warp_slot * (32 * HN * 2);
+        const uint32_t wstage = smem_u32(c.stage) + (uint32_t)(c.warp_slot * (32 * HN * 2));
         uint32_t hi[HN / 2];
 #pragma unroll
         for (int i = 0; i < HN / 2; ++i) {
@@ -737,6 +896,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         c.scratch = epi_scratch;
         c.stage = epi_stage;
         c.nthreads = NUM_EPI_WARPS * 32;
+        c.sub = 0;
+        c.nsub = 1;
         uint32_t cc = 0;
         int runs = 0;  // epilogue invocations so far (parity of the smem scratch buffers)
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
@@ -776,7 +937,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
                 }
-                Epi::template run<HN>(ep, c, acc);
+                typename Epi::Tile tile_state = Epi::begin_tile(ep, c);
+                Epi::template run<HN>(ep, c, tile_state, acc);
             } else {
                 // two row blocks, one chunk: drain and process them one after the other
                 const uint32_t buf = cc & 1;
@@ -803,7 +965,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // both row blocks drained
                     }
-                    Epi::template run<HN>(ep, c, acc);
+                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c);
+                    Epi::template run<HN>(ep, c, tile_state, acc);
                 }
                 ++cc;
             }

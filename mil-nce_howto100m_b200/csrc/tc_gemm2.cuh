@@ -238,6 +238,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         c.scratch = epi_scratch;
         c.stage = epi_stage;
         c.nthreads = NUM_EPI_WARPS * 32;
+        c.nsub = 2;
         uint32_t cc = 0;
         int runs = 0;
         for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
@@ -246,11 +247,13 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             c.m_blk = m_blk * 2 + (int)rank;   // 128-row block index of this CTA's rows
             c.m0 = c.m_blk * BLOCK_M;
             const uint32_t buf = cc & 1;
+            typename Epi::Tile tile_state = Epi::begin_tile(ep, c);  // overlaps the wait below
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
 #pragma unroll 1
             for (int nb = 0; nb < 2; ++nb) {   // the 256-wide tile as two 128-wide column blocks
                 c.n_blk = n_blk * 2 + nb;
+                c.sub = nb;
                 c.n0 = c.n_blk * 128 + c.half * HN;
                 c.par = runs & 1;
                 ++runs;
@@ -269,7 +272,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
                 }
-                Epi::template run<HN>(ep, c, acc);
+                Epi::template run<HN>(ep, c, tile_state, acc);
             }
         }
     }
