@@ -69,12 +69,14 @@ int milnce_forward(const void *video, const void *text, int B, int K, int D, int
 
 /* Backward.  den must hold all B entries (all-gathered when sharded); nom
  * needs entries [i0, i0+n).  grad_loss[0] is d(objective)/d(loss), read on
- * the device.  Outputs are float32: dvideo (n, D) = rows [i0, i0+n) of
- * d loss/d video, dtext (n*K, D) = rows [i0*K, (i0+n)*K) of d loss/d text.
+ * the device.  Outputs: dvideo (n, D) = rows [i0, i0+n) of d loss/d video,
+ * dtext (n*K, D) = rows [i0*K, (i0+n)*K) of d loss/d text, written as
+ * grad_dtype (B200HEAD_F32 or B200HEAD_BF16: autograd hands back gradients in
+ * the dtype of the inputs, so a bf16 caller gets them without a conversion pass).
  * reuse_forward_ws != 0 promises that `workspace` is untouched since a
  * milnce_forward call with the same inputs (skips re-staging the operands). */
 int milnce_backward(const void *video, const void *text, const float *den, const float *nom,
-                    const float *grad_loss, float *dvideo, float *dtext,
+                    const float *grad_loss, void *dvideo, void *dtext, int grad_dtype,
                     int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
                     void *workspace, size_t workspace_bytes, void *stream);
 

@@ -68,7 +68,7 @@ def _declare(lib):
     lib.milnce_forward.restype = i32
     lib.milnce_forward.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, fp, fp, fp, vp, sz, vp]
     lib.milnce_backward.restype = i32
-    lib.milnce_backward.argtypes = [vp, vp, fp, fp, fp, fp, fp, i32, i32, i32, i32, i32, i32, i32,
+    lib.milnce_backward.argtypes = [vp, vp, fp, fp, fp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32,
                                     vp, sz, vp]
     lib.milnce_forward_shard.restype = i32
     lib.milnce_forward_shard.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, fp, fp, fp, vp, sz, vp]
@@ -96,8 +96,10 @@ def load():
     """Return the loaded library, building it first if it is missing or stale."""
     global _lib
     if _lib is None:
-        build()
-        lib = ctypes.CDLL(LIB_PATH)
+        alt = os.environ.get("B200HEAD_LIB")  # developer hook: an experimental build of the same sources
+        if not alt:
+            build()
+        lib = ctypes.CDLL(alt or LIB_PATH)
         _declare(lib)
         _lib = lib
     return _lib

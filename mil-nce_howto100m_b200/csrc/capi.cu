@@ -2,6 +2,8 @@
 #include <mutex>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -94,4 +96,14 @@ int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t
 }  // namespace b200
 
 extern "C" const char *b200head_last_error(void) { return b200::get_error(); }
-extern "C" int b200head_version(void) { return 1; }
+extern "C" int b200head_version(void) { return 2; }
+
+namespace b200 {
+bool pdl_enabled() {
+    static const bool v = [] {
+        const char *e = getenv("B200HEAD_PDL");
+        return !(e && e[0] == '0');
+    }();
+    return v;
+}
+}  // namespace b200

@@ -26,6 +26,29 @@ int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Launch with programmatic stream serialization: the grid may be scheduled while the previous
+// kernel of the stream is still draining, so its prologue (barrier set-up, TMEM allocation,
+// descriptor prefetch) and the launch latency overlap that kernel's tail.  Every kernel launched
+// this way executes griddepcontrol.wait (tc::pdl_wait) before it touches global memory, which
+// blocks until the previous grid has completed and its writes are visible.  B200HEAD_PDL=0 in the
+// environment falls back to plain launches (for A/B timing).
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 #define B200_CUDA_OK(expr)                                                                 \
     do {                                                                                   \
         cudaError_t _e = (expr);                                                           \

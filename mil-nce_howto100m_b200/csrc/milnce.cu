@@ -61,7 +61,7 @@ struct Plan {
     long long ld_g, ld_gt;   // G (n, P*BK), Gt (n*K, P*B)
     long long ld_g2;         // G2 (B, n*K) for the sharded bf16 backward
     int nb_r, nb_c;          // n-blocks of pass R (over BK columns) and pass C (over B columns)
-    int nb_cl;               // 128-row blocks of the owned rows
+    int nb_cl;               // 32-row blocks of the owned rows
     int cg;                  // columns per column statistic: K when the epilogue pre-sums the K candidates, else 1
     int chunk_s, chunk_g;    // k-blocks per tensor-core accumulation chunk (S passes / grad GEMMs)
     size_t off_scal, off_vk, off_tk, off_vt, off_tt, off_pr, off_pc, off_diff, off_bsum, off_g, off_gt, total;
@@ -85,8 +85,9 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     // one row partial per epilogue warp column part; bf16 mode runs 256-wide pair tiles (all written)
     p.nb_r = tc::EpiRowCol::PARTS * ((p.P == 1) ? (int)((p.BK + 255) / 256) : (int)((p.BK + BLOCK_N - 1) / BLOCK_N));
     p.cg = (p.P == 1 && (K == 2 || K == 4 || K == 8)) ? K : 1;
-    // one column partial per 128-row block; bf16 mode runs 256-row tiles (both halves are written)
-    p.nb_c = (p.P == 1) ? 2 * ((B + 255) / 256) : (B + 127) / 128;
+    // one column partial per 32-row block (one per epilogue warp quarter); bf16 mode runs 256-row
+    // tiles, and every 32-row block of a tile is written
+    p.nb_c = (p.P == 1) ? 8 * ((B + 255) / 256) : 4 * ((B + 127) / 128);
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 1024); return r; };
     p.off_scal = take(sizeof(Scalars));
@@ -95,7 +96,7 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.off_vt = take((size_t)D * p.ld_vt * 2);
     p.off_tt = take((size_t)D * p.ld_tt * 2);
     p.off_pr = take((size_t)p.nb_r * n * 4);
-    p.nb_cl = 2 * ((n + 255) / 256);  // row blocks of the owned rows (rows-only sharding)
+    p.nb_cl = 8 * ((n + 255) / 256);  // 32-row blocks of the owned rows (rows-only sharding)
     p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) / p.cg * 4);
     p.off_diff = take((size_t)n * 4 * 2);  // den - nom, then the merged den
     p.off_bsum = take((size_t)((n + 31) / 32) * 8);  // per-block partial sums of den - nom (double)
@@ -163,6 +164,8 @@ __global__ void scalars_forward_kernel(Scalars *s) {
 // one block: gradient scales + the range of den (decides the one-exp path of EpiG)
 __global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, const float *den, int B) {
     __shared__ float smin[32], smax[32];
+    tc::pdl_wait();
+    tc::pdl_trigger();
     float lo = INFINITY, hi = -INFINITY;
     for (int i = threadIdx.x; i < B; i += blockDim.x) {
         const float d = den[i];
@@ -249,6 +252,8 @@ struct StageSide {
 __global__ void __launch_bounds__(256)
 stage_bf16_kernel(StageSide sv, StageSide stx, int tiles_v, int D, Scalars *scal) {
     __shared__ __half tile[64][64 + 2];  // +2 halves: conflict-free column reads
+    tc::pdl_wait();
+    tc::pdl_trigger();
     const float s_v = pow2_scale(scal->absmax_bits[0]), s_t = pow2_scale(scal->absmax_bits[1]);
     if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {  // nobody reads these in this kernel
         scal->s_video = s_v;
@@ -317,9 +322,11 @@ __device__ __forceinline__ float warp_sum(float v) {
 //   - nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs on the original values
 //     (loss.py:13-15), for the samples in [i0, i0+n) when nom != nullptr.
 // D % 8 == 0 and 16-byte aligned rows (checked by the caller).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)
 prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *__restrict__ text, int B,
                  int K, int D, int i0, int n, float *__restrict__ nom, unsigned int *absmax_bits) {
+    tc::pdl_wait();
+    tc::pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     float mv = 0.f, mt = 0.f;
@@ -344,9 +351,11 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
         const bool want_nom = (nom != nullptr) && i >= i0 && i < i0 + n;
         const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
         float pm = -INFINITY, ps = 0.f;
+#pragma unroll 2
         for (int k = 0; k < K; ++k) {
             const uint4 *trow = reinterpret_cast<const uint4 *>(text + ((size_t)i * K + k) * D);
             float acc = 0.f;
+#pragma unroll 2
             for (int c = lane; c < D / 8; c += 32) {
                 float fv[8], ft[8];
                 unpack8(__ldg(vrow + c), fv);  // re-read per candidate: 1 KB per warp, stays in L1
@@ -413,6 +422,8 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     constexpr int NW = 32;
     __shared__ float sm[NW][32], ss[NW][32];
     __shared__ bool is_last;
+    tc::pdl_wait();
+    tc::pdl_trigger();
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     const int w = blockIdx.x * 32 + lane;
     float m = -INFINITY, s = 0.f;
@@ -425,10 +436,27 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
         }
     };
     if (w < n) {
-        for (int t = wp; t < nb_r; t += NW) push(part_r[(size_t)t * n + w]);
+        // batches of four independent loads, then the (serial) merges
+        for (int t = wp; t < nb_r; t += 4 * NW) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                v[u] = (t + u * NW < nb_r) ? __ldg(part_r + (size_t)(t + u * NW) * n + w) : -INFINITY;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) push(v[u]);
+        }
         const size_t nk = (size_t)n * kc;
-        for (int t = wp; t < nb_c; t += NW)
-            for (int k = 0; k < kc; ++k) push(part_c[(size_t)t * nk + (size_t)w * kc + k]);
+        for (int k = 0; k < kc; ++k) {
+            const float *pc = part_c + (size_t)w * kc + k;
+            for (int t = wp; t < nb_c; t += 4 * NW) {
+                float v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[u] = (t + u * NW < nb_c) ? __ldg(pc + (size_t)(t + u * NW) * nk) : -INFINITY;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) push(v[u]);
+            }
+        }
     }
     sm[wp][lane] = m;
     ss[wp][lane] = s;
@@ -533,11 +561,20 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     return 0;
 }
 
+// B200HEAD_ASTAT=0 in the environment selects the streaming kernel for the similarity GEMMs too
+// (A/B timing).
+bool astat_enabled() {
+    static const bool v = [] {
+        const char *e = getenv("B200HEAD_ASTAT");
+        return !(e && e[0] == '0');
+    }();
+    return v;
+}
+
 // bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.
 template <class Epi, bool A_MN = false, bool N_FAST = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                  const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
-    using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
     CUtensorMap ma, mb;
     int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
                   : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
@@ -545,14 +582,28 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     if (rc) return rc;
     rc = b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, tc::PAIR_N / 2);
     if (rc) return rc;
-    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST>;
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
     const int max_pairs = num_sms() / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
     tc::GemmShape shape{M, N, Kd, 0};
-    kern<<<2 * pairs, tc::num_threads<Epi>(), L::TOTAL, stream>>>(ma, mb, shape, ep);
-    B200_LAUNCH_OK(what);
+    (void)what;
+    // short reductions with an epilogue-heavy functor: keep A resident, stream only B
+    constexpr bool CAN_ASTAT = !A_MN && !std::is_same<Epi, tc::EpiStore>::value;
+    if constexpr (CAN_ASTAT) {
+        if (Kd <= tc::ASTAT_MAX_K_ITERS * tc::BLOCK_K && astat_enabled()) {
+            using LA = tc::SmemLayoutAS<Epi::STAGE_BYTES>;
+            auto kern = tc::gemm_tn_2cta_astat_kernel<Epi>;
+            B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, LA::TOTAL));
+            B200_CUDA_OK(b200::launch_pdl(kern, dim3(2 * pairs), dim3(tc::num_threads<Epi>()), LA::TOTAL, stream, ma,
+                                          mb, shape, ep));
+            return 0;
+        }
+    }
+    using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
+    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    B200_CUDA_OK(b200::launch_pdl(kern, dim3(2 * pairs), dim3(tc::num_threads<Epi>()), L::TOTAL, stream, ma, mb,
+                                  shape, ep));
     return 0;
 }
 
@@ -570,12 +621,13 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
         if (fast) {
             const int wpb = 8;
             const int blocks = std::min((p.B + wpb - 1) / wpb, 8 * num_sms());
-            prep_bf16_kernel<<<blocks, wpb * 32, 0, st>>>(video, text, p.B, p.K, p.D, p.i0, p.n, nom,
-                                                          sc->absmax_bits);
+            B200_CUDA_OK(b200::launch_pdl(prep_bf16_kernel, dim3(blocks), dim3(wpb * 32), 0, st, video, text, p.B,
+                                          p.K, p.D, p.i0, p.n, nom, sc->absmax_bits));
             const int tiles_v = (p.B + 63) / 64, tiles_t = (int)((p.BK + 63) / 64);
             StageSide sv{video, p.B, vk_, p.ld_vk, vt_, p.ld_vt};
             StageSide stx{text, (int)p.BK, tk_, p.ld_tk, tt_, p.ld_tt};
-            stage_bf16_kernel<<<dim3(tiles_v + tiles_t, (p.D + 63) / 64), 256, 0, st>>>(sv, stx, tiles_v, p.D, sc);
+            B200_CUDA_OK(b200::launch_pdl(stage_bf16_kernel, dim3(tiles_v + tiles_t, (p.D + 63) / 64), dim3(256), 0,
+                                          st, sv, stx, tiles_v, p.D, sc));
         }
     }
     if (!fast) {
@@ -682,15 +734,15 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         if (rc) return rc;
     }
     MergeFin fin{nom, den, diff, reinterpret_cast<double *>(ws + p.off_bsum), &sc->ticket, loss, p.i0, p.B};
-    merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, pc, p.K / p.cg, p.n, p.nb_r, p.nb_c, nullptr,
-                                                            fin);
+    B200_CUDA_OK(b200::launch_pdl(merge_partials_kernel, dim3((p.n + 31) / 32), dim3(1024), 0, st, pr, pc,
+                                  p.K / p.cg, p.n, p.nb_r, p.nb_c, (float *)nullptr, fin));
     B200_LAUNCH_OK("milnce finalize");
     return 0;
 }
 
 template <typename T>
 int backward_impl(const Plan &p, const T *video, const T *text, const float *den, const float *nom,
-                  const float *grad_loss, float *dvideo, float *dtext, int reuse, uint8_t *ws,
+                  const float *grad_loss, void *dvideo, void *dtext, int grad_bf16, int reuse, uint8_t *ws,
                   cudaStream_t st) {
     int rc;
     if (!reuse) {
@@ -698,7 +750,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    scalars_backward_kernel<<<1, 1024, 0, st>>>(sc, grad_loss, den, p.B);
+    B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
@@ -716,7 +768,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                             "milnce backward row block");
     if (rc) return rc;
     // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
     rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
@@ -725,7 +777,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
     if (rc) return rc;
-    tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext};
+    tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext, grad_bf16};
     if (p.P == 1) {
         // dtext (n*K, D) = G[:, own columns]^T . V, reading G as an MN-major A operand:
         // nobody materialises G^T.  On one GPU (n == B) the G of the row block is the G needed.
@@ -789,13 +841,14 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
 int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
                         const float *den, const float *nom, const float *grad_loss, float *dvideo,
                         float *dtext_partial, int reuse, uint8_t *ws, cudaStream_t st) {
+    const int grad_bf16 = 0;
     int rc;
     if (!reuse) {
         rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    scalars_backward_kernel<<<1, 1024, 0, st>>>(sc, grad_loss, den, p.B);
+    B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
@@ -806,12 +859,12 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     rc = launch_gemm2<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
                                 st, "milnce backward (rows-only shard) G");
     if (rc) return rc;
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo};
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
     rc = launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
                                                  "milnce dvideo GEMM (shard)");
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
-    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext};
+    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext, 0};
     return launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd,
                                                   st, "milnce partial dtext GEMM (shard)");
 }
@@ -863,8 +916,8 @@ extern "C" int milnce_forward(const void *video, const void *text, int B, int K,
 }
 
 extern "C" int milnce_backward(const void *video, const void *text, const float *den,
-                               const float *nom, const float *grad_loss, float *dvideo,
-                               float *dtext, int B, int K, int D, int dtype, int i0, int n,
+                               const float *nom, const float *grad_loss, void *dvideo,
+                               void *dtext, int grad_dtype, int B, int K, int D, int dtype, int i0, int n,
                                int reuse_forward_ws, void *workspace, size_t workspace_bytes,
                                void *stream) {
     Plan p;
@@ -877,6 +930,11 @@ extern "C" int milnce_backward(const void *video, const void *text, const float 
         b200::set_error("milnce_backward: null pointer argument");
         return B200HEAD_ERR_ARG;
     }
+    if (grad_dtype != B200HEAD_F32 && grad_dtype != B200HEAD_BF16) {
+        b200::set_error("milnce_backward: grad_dtype must be B200HEAD_F32 or B200HEAD_BF16");
+        return B200HEAD_ERR_ARG;
+    }
+    const int gb = (grad_dtype == B200HEAD_BF16) ? 1 : 0;
     int rc = b200::check_device();
     if (rc) return rc;
     rc = check_common(p, workspace, workspace_bytes);
@@ -885,10 +943,19 @@ extern "C" int milnce_backward(const void *video, const void *text, const float 
     uint8_t *ws = (uint8_t *)workspace;
     if (dtype == B200HEAD_F32)
         return backward_impl<float>(p, (const float *)video, (const float *)text, den, nom, grad_loss,
-                                    dvideo, dtext, reuse_forward_ws, ws, st);
+                                    dvideo, dtext, gb, reuse_forward_ws, ws, st);
     return backward_impl<__nv_bfloat16>(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text,
-                                        den, nom, grad_loss, dvideo, dtext, reuse_forward_ws, ws, st);
+                                        den, nom, grad_loss, dvideo, dtext, gb, reuse_forward_ws, ws, st);
 }
+
+#ifdef B200_EPI_STAMP
+extern "C" int b200head_debug_stamps(long long *host, size_t count) {
+    const size_t have = sizeof(tc::g_stamp) / sizeof(long long);
+    B200_CUDA_OK(cudaDeviceSynchronize());
+    B200_CUDA_OK(cudaMemcpyFromSymbol(host, tc::g_stamp, sizeof(long long) * (count < have ? count : have)));
+    return 0;
+}
+#endif
 
 extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
                                     int lda, int ldb, int ldc, float alpha, void *stream) {
@@ -898,7 +965,7 @@ extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
     return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                      "gemm_tn_f16 test hook");
 }
@@ -911,7 +978,7 @@ extern "C" int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, in
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
     return launch_gemm<tc::EpiStore, true>(At, ldat, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                            "gemm_at_f16 test hook");
 }
@@ -924,7 +991,7 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
     return a_transposed ? launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep,
                                                                  (cudaStream_t)stream, "gemm2 test hook")
                         : launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep,

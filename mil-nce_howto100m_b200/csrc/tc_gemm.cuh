@@ -18,6 +18,7 @@
 // backward).  This replaces reference loss.py:11 (th.matmul) + :13-18.
 #pragma once
 #include <cuda.h>
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -74,6 +75,31 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
         if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 4000000000ull) __trap();
     }
+}
+
+// Warp-uniform wait: all 32 lanes poll and leave together, so the code after it stays convergent
+// (the single-lane form makes ptxas wrap every tcgen05/TMA issue in an elect + R2UR + retry loop,
+// ~25 instructions per MMA, and the issuing thread then cannot keep the tensor core fed while the
+// epilogue warps compete for its scheduler: measured 5100-6400 instead of 4250 cycles per tile).
+__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity) {
+    if (__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) return;
+    uint64_t t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+        if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > 4000000000ull) __trap();
+    }
+}
+// true in exactly one lane of a fully active warp
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
 }
 
 __device__ __forceinline__ void fence_barrier_init() {
@@ -141,6 +167,14 @@ __device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr, uint32_t l
     d |= (uint64_t)2 << 61;
     return d;
 }
+// The same descriptors as (low word, high word): the high word is a constant, so stepping through
+// K is one 32-bit add on the low word.
+constexpr uint32_t SMEM_DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO, version, SWIZZLE_128B
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t saddr) { return ((saddr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint32_t smem_desc_mn_lo(uint32_t saddr, uint32_t lbo_bytes) {
+    return ((saddr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+
 // kind::f16 instruction descriptor: fp16 x fp16 -> fp32; a_mn = 1 selects an
 // MN-major A operand (bit 15), B is always K-major here.
 __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int a_mn = 0) {
@@ -185,9 +219,32 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// programmatic dependent launch (see b200::launch_pdl): wait for the previous grid of the stream,
+// and allow the next one to be scheduled early.  No-ops under a plain launch.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Development instrumentation (variant builds with -DB200_EPI_STAMP only): clock64 stamps of CTA 0's
+// warps for the first 64 tiles, read back with b200head_debug_stamps (profiles/microbench/epi_timeline.py).
+#ifdef B200_EPI_STAMP
+constexpr int STAMP_KINDS = 3, STAMP_WARPS = 20, STAMP_TILES = 64, STAMP_SLOTS = 16;
+__device__ long long g_stamp[STAMP_KINDS * STAMP_WARPS * STAMP_TILES * STAMP_SLOTS];
+__device__ __forceinline__ void epi_stamp(int kind, int tile, int slot) {
+    if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && tile < STAMP_TILES)
+        g_stamp[((kind * STAMP_WARPS + (threadIdx.x >> 5)) * STAMP_TILES + tile) * STAMP_SLOTS + slot] = clock64();
+}
+#else
+__device__ __forceinline__ void epi_stamp(int, int, int) {}
+#endif
+
 __device__ __forceinline__ float fast_exp2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float fast_log2(float x) {  // one MUFU; log2(0) = -inf; |error| ~ 1e-7
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
 
@@ -263,6 +320,7 @@ struct EpiCtx {
     uint8_t *stage;    // Epi::STAGE_BYTES bytes of smem (this warp's slice starts at warp_slot)
     int warp_slot;     // 0 .. 4*PARTS-1
     int sub, nsub;     // column sub-block of the tile this run covers, and how many a tile has (1 or 2)
+    int dbg_tile;      // tile counter of this CTA (instrumented builds)
 };
 constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 // Every functor receives the finished fp32 accumulator (its row, its column half) in
@@ -271,18 +329,22 @@ constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 
 // ---- plain store: C = alpha * acc (dvideo / dtext GEMMs, and the test hook) ----
 struct EpiStore {
+    static constexpr int STAMP_KIND = 0;
     static constexpr int STAGE_BYTES = 0;
     static constexpr int PARTS = 2;
     struct Params {
-        float *C;
+        void *C;  // float32, or bfloat16 when out_bf16 != 0
         long long ldc;
         float alpha;
         const float *alpha_dev;  // optional device scalar multiplied into alpha
+        int out_bf16;
     };
     struct Tile {
         float alpha;
     };
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &) {
+    struct Pre {};
+    __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &, const Pre &) {
         Tile t;
         t.alpha = p.alpha;
         if (p.alpha_dev) t.alpha *= __ldg(p.alpha_dev);
@@ -297,7 +359,26 @@ struct EpiStore {
         for (int ch = 0; ch < HN / 32; ++ch) {
             const int col0 = c.n0 + ch * 32;
             if (col0 >= c.N) break;
-            float *dst = p.C + (long long)row * p.ldc + col0;
+            if (p.out_bf16) {
+                __nv_bfloat16 *dst = reinterpret_cast<__nv_bfloat16 *>(p.C) + (long long)row * p.ldc + col0;
+                if (col0 + 32 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 8) {
+                        const int e = ch * 32 + i;
+                        __nv_bfloat162 h[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            h[u] = __floats2bfloat162_rn(acc[e + 2 * u] * alpha, acc[e + 2 * u + 1] * alpha);
+                        *reinterpret_cast<uint4 *>(dst + i) = *reinterpret_cast<uint4 *>(h);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (col0 + i < c.N) dst[i] = __float2bfloat16_rn(acc[ch * 32 + i] * alpha);
+                }
+                continue;
+            }
+            float *dst = reinterpret_cast<float *>(p.C) + (long long)row * p.ldc + col0;
             if (col0 + 32 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
@@ -366,12 +447,16 @@ constexpr float TINY_SUM = 7.8886090522101181e-31f;  // 2^-100
 // are added inside the thread before the cross-lane reduction: 32/G - 1 + log2(G) shuffles per 32
 // columns instead of 31.  G = 1 keeps one statistic per column (any K).
 //   part_row[PARTS*(n_blk/nsub) + part][row] = log sum_{n in part of the tile} exp(s[row, n])
-//   part_col[m_blk][col / G]                 = log sum_{m in tile, n in group} exp(s[m, n])
+//   part_col[4*m_blk + q][col / G]           = log sum_{m in 32-row block q of the tile, n in group} exp(s[m, n])
 template <int G>
 struct EpiRowColT {
     static_assert(G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32, "group size");
+    static constexpr int STAMP_KIND = 1;
     static constexpr int STAGE_BYTES = 0;
-    static constexpr int PARTS = 2;
+#ifndef B200_ROWCOL_PARTS
+#define B200_ROWCOL_PARTS 2
+#endif
+    static constexpr int PARTS = B200_ROWCOL_PARTS;
     static constexpr int NG = 32 / G;  // statistics per 32 columns
     struct Params {
         float *part_row;  // may be null: skip the row statistic
@@ -382,12 +467,15 @@ struct EpiRowColT {
     };
     struct Tile {
         float sc;
-        float row_run;  // row statistic carried across the column sub-blocks of one tile (log2)
+        float row_m, row_s;  // row statistic carried across the column sub-blocks of one tile: 2^row_m * row_s
     };
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &) {
+    struct Pre {};
+    __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &, const Pre &) {
         Tile t;
         t.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
-        t.row_run = -INFINITY;
+        t.row_m = -INFINITY;
+        t.row_s = 0.f;
         return t;
     }
     template <int HN>
@@ -403,99 +491,117 @@ struct EpiRowColT {
             for (int i = 0; i < HN; ++i)
                 if (c.n0 + i >= c.N) acc[i] = -INFINITY;
         }
-        float tmax = -INFINITY;
+        // (four independent chains: with two or four warps per scheduler a 64-long dependent chain
+        // of 4-cycle operations is not hidden)
+        float tm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < HN; ++i) tmax = fmaxf(tmax, acc[i]);
+        for (int i = 0; i < HN; ++i) tm[i & 3] = fmaxf(tm[i & 3], acc[i]);
+        float tmax = fmaxf(fmaxf(tm[0], tm[1]), fmaxf(tm[2], tm[3]));
         tmax *= sc;  // sc > 0
         const float wmax = warp_max_f(row_ok ? tmax : -INFINITY);
         float wl[HN / 32];
-        float row_lse = -INFINITY;
-        if (wmax > -INFINITY) {  // warp-uniform; false only for fully masked sub-tiles
-            float rs = 0.f;
+        float pm = -INFINITY, ps = 0.f;  // this run's row statistic as (shift, sum): log2 domain
+        if (wmax > -INFINITY) {          // warp-uniform; false only for fully masked sub-tiles
+            // Phase 1, all independent work: the exponentials and the in-thread group sums.
+            // Phase 2: the cross-lane butterflies of all 32-column chunks (independent chains).
+            // Phase 3: logarithms and ONE vote for the rare exact path.  (A vote + branch after
+            // every chunk put a ~450-cycle serial chain - butterfly, log2f, vote - between chunks
+            // that two warps per scheduler could not hide.)
+            float rsum[4] = {0.f, 0.f, 0.f, 0.f};
+            float g[HN / 32][NG];
 #pragma unroll
             for (int ch = 0; ch < HN / 32; ++ch) {
-                float g[NG];
 #pragma unroll
                 for (int u = 0; u < NG; ++u) {
-                    float gs = 0.f;
+                    float e[G];
 #pragma unroll
                     for (int v = 0; v < G; ++v)
-                        gs += row_ok ? fast_exp2(fmaf(acc[ch * 32 + u * G + v], sc, -wmax)) : 0.f;
-                    g[u] = gs;
-                    rs += gs;
-                }
-                wl[ch] = -INFINITY;
-                if (want_col) {
-                    const float cs = warp_transpose_sum<NG>(g, lane);  // lane l: group l % NG
-                    wl[ch] = wmax + log2f(cs);
-                    const bool valid = (c.n0 + ch * 32 + (lane % NG) * G) < c.N;
-                    if (__any_sync(0xffffffffu, valid && cs < TINY_SUM)) {
-                        // exact path for this 32 x 32 block: every column with its own maximum,
-                        // the G columns of a group merged on the fly (uniform across lanes)
-                        float gm = -INFINITY, gsum = 0.f;
+                        e[v] = row_ok ? fast_exp2(fmaf(acc[ch * 32 + u * G + v], sc, -wmax)) : 0.f;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float y = row_ok ? acc[ch * 32 + j] * sc : -INFINITY;
-                            const float cm = warp_max_f(y);
-                            const float e = (cm > -INFINITY) ? fast_exp2(y - cm) : 0.f;
-                            const float s = warp_sum_f(e);
-                            if (cm > gm) {
-                                gsum = gsum * fast_exp2(gm - cm) + s;  // gm = -inf: 2^-inf = 0
-                                gm = cm;
-                            } else if (cm > -INFINITY) {
-                                gsum += s * fast_exp2(cm - gm);
-                            }
-                            if ((j % G) == G - 1) {
-                                if ((lane % NG) == j / G) wl[ch] = (gm > -INFINITY) ? gm + log2f(gsum) : -INFINITY;
-                                gm = -INFINITY;
-                                gsum = 0.f;
-                            }
+                    for (int w = G / 2; w > 0; w >>= 1)  // pairwise tree
+#pragma unroll
+                        for (int v = 0; v < w; ++v) e[v] += e[v + w];
+                    g[ch][u] = e[0];
+                    rsum[u & 3] += e[0];
+                }
+            }
+            bool bad = false;
+            if (want_col) {
+                float cs[HN / 32];
+#pragma unroll
+                for (int ch = 0; ch < HN / 32; ++ch) cs[ch] = warp_transpose_sum<NG>(g[ch], lane);  // lane l: group l % NG
+#pragma unroll
+                for (int ch = 0; ch < HN / 32; ++ch) {
+                    wl[ch] = wmax + fast_log2(cs[ch]);
+                    bad |= ((c.n0 + ch * 32 + (lane % NG) * G) < c.N) && cs[ch] < TINY_SUM;
+                }
+            } else {
+#pragma unroll
+                for (int ch = 0; ch < HN / 32; ++ch) wl[ch] = -INFINITY;
+            }
+            if (__any_sync(0xffffffffu, bad)) {
+                // exact path: every column with its own maximum, the G columns of a group merged
+                // on the fly (uniform across lanes)
+#pragma unroll
+                for (int ch = 0; ch < HN / 32; ++ch) {
+                    float gm = -INFINITY, gsum = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float y = row_ok ? acc[ch * 32 + j] * sc : -INFINITY;
+                        const float cm = warp_max_f(y);
+                        const float e = (cm > -INFINITY) ? fast_exp2(y - cm) : 0.f;
+                        const float s2 = warp_sum_f(e);
+                        if (cm > gm) {
+                            gsum = gsum * fast_exp2(gm - cm) + s2;  // gm = -inf: 2^-inf = 0
+                            gm = cm;
+                        } else if (cm > -INFINITY) {
+                            gsum += s2 * fast_exp2(cm - gm);
+                        }
+                        if ((j % G) == G - 1) {
+                            if ((lane % NG) == j / G) wl[ch] = (gm > -INFINITY) ? gm + log2f(gsum) : -INFINITY;
+                            gm = -INFINITY;
+                            gsum = 0.f;
                         }
                     }
                 }
             }
-            row_lse = wmax + log2f(rs);
-            if (rs < TINY_SUM && tmax > -INFINITY) {  // exact per-row path
+            pm = wmax;
+            ps = (rsum[0] + rsum[1]) + (rsum[2] + rsum[3]);
+            if (ps < TINY_SUM && tmax > -INFINITY) {  // exact per-row path
                 float r2 = 0.f;
 #pragma unroll
                 for (int i = 0; i < HN; ++i) r2 += fast_exp2(fmaf(acc[i], sc, -tmax));
-                row_lse = tmax + log2f(r2);
+                pm = tmax;
+                ps = r2;
             }
         } else {
 #pragma unroll
             for (int ch = 0; ch < HN / 32; ++ch) wl[ch] = -INFINITY;
         }
         if (p.part_row != nullptr) {
-            // one row partial per (tile, column part): merge the tile's column sub-blocks first
-            float acc_lse = row_lse;
+            // one row partial per (tile, column part): the tile's column sub-blocks are merged as
+            // (shift, sum) pairs, one logarithm at the end
+            float m = pm, sum = ps;
             if (c.sub > 0) {
-                const float m = fmaxf(t.row_run, row_lse);
-                acc_lse = (m > -INFINITY) ? m + log2f(fast_exp2(t.row_run - m) + fast_exp2(row_lse - m)) : m;
+                m = fmaxf(t.row_m, pm);
+                sum = (m > -INFINITY) ? t.row_s * fast_exp2(t.row_m - m) + ps * fast_exp2(pm - m) : 0.f;
             }
-            t.row_run = acc_lse;
+            t.row_m = m;
+            t.row_s = sum;
             if (c.sub == c.nsub - 1 && row_ok)
-                p.part_row[(long long)((c.n_blk >> (c.nsub - 1)) * PARTS + c.half) * p.ldr + row] = acc_lse * LN2;
+                p.part_row[(long long)((c.n_blk >> (c.nsub - 1)) * PARTS + c.half) * p.ldr + row] =
+                    (m + fast_log2(sum)) * LN2;  // sum = 0 -> -inf
         }
-        if (want_col) {
-            // merge the four lane-quarters' partials through smem (double-buffered by tile parity)
+        if (want_col && lane < NG) {
+            // one column partial per (32-row block, column group): rows 4*m_blk + q of part_col.
+            // (merging the four lane quarters of the CTA here needed a barrier across all epilogue
+            // warps per run; the merge kernel reads four times as many rows instead)
             constexpr int NGB = 128 / G;  // statistics per 128-column block
-            float *buf = c.scratch + c.par * (4 * 128);
-            if (lane < NG) {
 #pragma unroll
-                for (int ch = 0; ch < HN / 32; ++ch)
-                    buf[c.q * 128 + (c.half * HN + ch * 32) / G + lane] = wl[ch];
-            }
-            epi_bar_sync(c.nthreads);
-            if (c.etid < NGB) {
-                const float v0 = buf[c.etid], v1 = buf[128 + c.etid], v2 = buf[256 + c.etid],
-                            v3 = buf[384 + c.etid];
-                const float m = fmaxf(fmaxf(v0, v1), fmaxf(v2, v3));
-                float out = -INFINITY;
-                if (m > -INFINITY)
-                    out = (m + log2f(fast_exp2(v0 - m) + fast_exp2(v1 - m) + fast_exp2(v2 - m) +
-                                     fast_exp2(v3 - m))) * LN2;
-                if (c.n_blk * 128 + c.etid * G < c.N)
-                    p.part_col[(long long)c.m_blk * p.ldc + c.n_blk * NGB + c.etid] = out;
+            for (int ch = 0; ch < HN / 32; ++ch) {
+                const int gi = (c.half * HN + ch * 32) / G + lane;  // group within the 128-column block
+                if (c.n_blk * 128 + gi * G < c.N)
+                    p.part_col[(long long)(c.m_blk * 4 + c.q) * p.ldc + c.n_blk * NGB + gi] = wl[ch] * LN2;
             }
         }
     }
@@ -519,6 +625,7 @@ struct GFast {
     const float *mid_log2_dev;
 };
 struct EpiG {
+    static constexpr int STAMP_KIND = 2;
     static constexpr int STAGE_BYTES = 4 * 32 * 128 * 2;  // 32 KB: a 128 x 128 fp16 block
     static constexpr int PARTS = 4;
     struct Params {
@@ -595,44 +702,62 @@ struct EpiG {
         bool fast;
         float mid, sc, dr13, ar;
         int n_lo, n_hi;  // columns whose sample is one of this row block's samples: [n_lo, n_hi)
+        float cf[4];     // per-lane column entries of the factor table, [sub * HN/32 + h]
     };
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c) {
+    // Raw per-sample values of one tile, loaded one tile AHEAD (preload for tile t+1 is issued
+    // before the runs of tile t): the den lookups were the top stall of this epilogue (ncu source
+    // page: long-scoreboard waits at the table build and at begin_tile).
+    struct Pre {
+        float den_r;
+        float den_c[4];
+    };
+    // m0: first row of the 128-row block; n_blk0: first 128-column block of the tile
+    __device__ static Pre preload(const Params &p, const EpiCtx &c, int m0, int n_blk0) {
+        Pre q;
+        const int HN = 128 / PARTS;
+        q.den_r = __ldg(p.den + p.rdiv.div(p.row_off + min(m0 + c.tid, c.M - 1)));
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+#pragma unroll
+            for (int h = 0; h < HN / 32; ++h) {
+                const int n = (n_blk0 + s) * 128 + c.half * HN + h * 32 + c.lane;
+                q.den_c[s * (HN / 32) + h] =
+                    (s < c.nsub && n < c.N) ? __ldg(p.den + p.cdiv.div(p.col_off + n)) : INFINITY;
+            }
+        return q;
+    }
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c, const Pre &q) {
         Tile t;
         t.fast = __ldg(p.fast.flag_dev) != 0;
         t.mid = __ldg(p.fast.mid_log2_dev);
         t.sc = __ldg(p.scale_dev) * LOG2E;
-        const int row = c.m0 + c.tid;
-        const int rs = p.rdiv.div(p.row_off + min(row, c.M - 1));
-        const float dr = __ldg(p.den + rs) * LOG2E;
+        const float dr = q.den_r * LOG2E;
         t.dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
         t.ar = t.fast ? fast_exp2(dr - t.mid) : 0.f;
         const int rs_lo = p.rdiv.div(p.row_off + c.m0);
         const int rs_hi = p.rdiv.div(p.row_off + min(c.m0 + BLOCK_M, c.M) - 1);
         t.n_lo = rs_lo * p.cdiv.d - p.col_off;
         t.n_hi = (rs_hi + 1) * p.cdiv.d - p.col_off;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float dc = q.den_c[i] * LOG2E;  // masked column: +inf -> factor 0 / exponent -inf
+            t.cf[i] = t.fast ? fast_exp2(t.mid - dc) : dc;
+        }
         return t;
     }
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
         static_assert(HN == 64 || HN == 32, "staging layout: 64 or 32 columns per warp");
+        static_assert(HN == 128 / PARTS, "preload assumes the kernel's column split");
         const bool fast = t.fast;
-        const float mid = t.mid;
-        // per-column factors of this warp's 64 columns, in the warp's own 256 bytes of smem:
-        // no CTA-wide barrier (a shared table made all eight warps wait for the slowest den load)
+        // per-column factors of this warp's columns, in the warp's own slice of smem: no CTA-wide
+        // barrier (a shared table made all warps wait for the slowest)
         const uint32_t tab = smem_u32(c.scratch) + (uint32_t)(c.warp_slot * HN * 4);
 #pragma unroll
-        for (int h = 0; h < HN / 32; ++h) {
-            const int n = c.n0 + h * 32 + c.lane;
-            float t;
-            if (n < c.N) {
-                const float dc = __ldg(p.den + p.cdiv.div(p.col_off + n)) * LOG2E;
-                t = fast ? fast_exp2(mid - dc) : dc;  // fast: column factor 2^(mid - den_c)
-            } else {
-                t = fast ? 0.f : INFINITY;  // masked column (never stored)
-            }
-            sts32f(tab + (uint32_t)((h * 32 + c.lane) * 4), t);
-        }
+        for (int h = 0; h < HN / 32; ++h)
+            sts32f(tab + (uint32_t)((h * 32 + c.lane) * 4), c.sub == 0 ? t.cf[h] : t.cf[HN / 32 + h]);
         __syncwarp();
+        epi_stamp(STAMP_KIND, c.dbg_tile, 8 + 2 * c.sub);  // table ready
         const float sc = t.sc, dr13 = t.dr13, ar = t.ar;
         // does this run touch the positives (row sample == column sample)?
         const bool diag_tile = (c.n0 < c.N) && (c.n0 < t.n_hi) && (c.n0 + HN > t.n_lo);
@@ -675,6 +800,7 @@ struct EpiG {
             }
         }
         __syncwarp();             // all lanes are done with this run's table
+        epi_stamp(STAMP_KIND, c.dbg_tile, 9 + 2 * c.sub);  // math done
         if (c.n0 >= c.N) return;  // warp-uniform: nothing of this half is inside the matrix
         const uint32_t wstage = smem_u32(c.stage) + (uint32_t)(c.warp_slot * (32 * HN * 2));
         uint32_t hi[HN / 2];
@@ -937,7 +1063,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
                 }
-                typename Epi::Tile tile_state = Epi::begin_tile(ep, c);
+                typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk));
                 Epi::template run<HN>(ep, c, tile_state, acc);
             } else {
                 // two row blocks, one chunk: drain and process them one after the other
@@ -965,7 +1091,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // both row blocks drained
                     }
-                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c);
+                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk));
                     Epi::template run<HN>(ep, c, tile_state, acc);
                 }
                 ++cc;

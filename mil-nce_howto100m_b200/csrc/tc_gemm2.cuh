@@ -75,6 +75,21 @@ __device__ __forceinline__ void umma_f16_2sm(uint32_t tmem_d, uint64_t adesc, ui
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// descriptors given as low words (see smem_desc_lo); `accumulate` is a compile-time-foldable flag
+__device__ __forceinline__ void umma_f16_2sm_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "mov.b64 da, {%1, %5};\n"
+        "mov.b64 db, {%2, %5};\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(SMEM_DESC_HI)
+        : "memory");
+}
 // arrives on `bar` (same offset) in both CTAs of the pair once the issued MMAs have retired
 __device__ __forceinline__ void umma_commit_2sm(uint64_t *bar) {
     const uint16_t mask = 3;
@@ -97,7 +112,10 @@ struct SmemLayout2 {
     static constexpr int STAGES_FIT = (MAX_SMEM - 1024 - TAIL_BYTES - EPI_STAGE_BYTES) / STAGE_BYTES;
     // epilogues that read per-sample vectors from global memory (EPI_STAGE_BYTES > 0: EpiG) keep
     // the ring at 4 stages so that ~55 KB of the SM stay L1 cache and those reads hit
-    static constexpr int STAGES_MAX = EPI_STAGE_BYTES > 0 ? 4 : 6;
+#ifndef B200_EPIG_STAGES
+#define B200_EPIG_STAGES 4
+#endif
+    static constexpr int STAGES_MAX = EPI_STAGE_BYTES > 0 ? B200_EPIG_STAGES : 6;
     static constexpr int STAGES = STAGES_FIT > STAGES_MAX ? STAGES_MAX : STAGES_FIT;
     static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_STAGE_BYTES + TAIL_BYTES + 1024;
     static_assert(STAGES >= 3, "pipeline too shallow");
@@ -155,6 +173,8 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     cluster_sync_all();  // the peer's barriers are initialised before anything signals them
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();     // everything above overlapped the previous kernel's tail; its results are needed now
+    pdl_trigger();  // the next kernel may be scheduled onto SMs as this grid's CTAs retire
 
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================
@@ -169,6 +189,14 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 for (int kb = 0; kb < k_iters; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
+#ifdef B200_EXP_NOTMA  // experiment: no operand traffic at all (results are garbage, timing only)
+                    mbar_arrive_cluster(lead_full);
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                    continue;
+#endif
                     mbar_expect_tx_cluster(lead_full, L::STAGE_BYTES);
                     uint8_t *sa = smem + stage * L::STAGE_BYTES;
                     if (A_MN) {
@@ -186,42 +214,43 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA, one thread) =====================
-        if (rank == 0 && lane == 0) {
+        // ===================== MMA issuer (leader CTA; the warp runs convergent, one lane issues) ====
+        if (rank == 0) {
             constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, A_MN ? 1 : 0);
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0;
+            const uint32_t smem_base = smem_u32(smem);
             for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
                 const uint32_t buf = cc & 1;
-                mbar_wait(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
+                mbar_wait_warp(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
                 tcgen05_fence_after();
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
                 const uint32_t tmem_d = tmem_base + buf * PAIR_N;
                 for (int kb = 0; kb < k_iters; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
+                    mbar_wait_warp(&full_bar[stage], phase);
                     tcgen05_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-                    const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
-                    if (A_MN) {
-                        const uint64_t adesc = make_smem_desc_mn(sa, L::A_BYTES / 2);
+                    const uint32_t sa = smem_base + (uint32_t)(stage * L::STAGE_BYTES);
+                    const uint32_t b_lo = smem_desc_lo(sa + L::A_BYTES);
+                    const uint32_t a_lo = A_MN ? smem_desc_mn_lo(sa, L::A_BYTES / 2) : smem_desc_lo(sa);
+                    constexpr uint32_t A_STEP = A_MN ? (UMMA_K * 128 / 16) : 2;
+                    if (elect_one()) {
+                        umma_f16_2sm_lo(tmem_d, a_lo, b_lo, idesc, (uint32_t)(kb != 0));
 #pragma unroll
-                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                            umma_f16_2sm(tmem_d, adesc + (uint64_t)(k * (UMMA_K * 128 / 16)),
-                                         bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
-                    } else {
-                        const uint64_t adesc = make_smem_desc(sa);
-#pragma unroll
-                        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                            umma_f16_2sm(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
-                                         idesc, (uint32_t)((kb | k) != 0));
+                        for (int k = 1; k < BLOCK_K / UMMA_K; ++k)
+                            umma_f16_2sm_lo(tmem_d, a_lo + k * A_STEP, b_lo + k * 2, idesc, 1u);
+                        umma_commit_2sm(&empty_bar[stage]);  // frees this slot in BOTH CTAs
                     }
-                    umma_commit_2sm(&empty_bar[stage]);  // frees this slot in BOTH CTAs
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit_2sm(&tfull_bar[buf]);  // accumulator complete, both CTAs
+                if (elect_one()) umma_commit_2sm(&tfull_bar[buf]);  // accumulator complete, both CTAs
+                __syncwarp();
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 2);
             }
         }
     } else {
@@ -241,15 +270,25 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         c.nsub = 2;
         uint32_t cc = 0;
         int runs = 0;
+        auto tile_m_blk = [&](int t) { return (N_FAST ? t / num_n : t % num_m) * 2 + (int)rank; };
+        auto tile_n_blk = [&](int t) { return N_FAST ? t % num_n : t / num_m; };
+        // per-sample values of a tile are loaded one tile ahead (Epi::preload), see EpiG
+        typename Epi::Pre pre{};
+        if (pair < num_tiles) pre = Epi::preload(ep, c, tile_m_blk(pair) * BLOCK_M, tile_n_blk(pair) * 2);
         for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
-            const int m_blk = N_FAST ? t / num_n : t % num_m;
-            const int n_blk = N_FAST ? t % num_n : t / num_m;
-            c.m_blk = m_blk * 2 + (int)rank;   // 128-row block index of this CTA's rows
+            const int n_blk = tile_n_blk(t);
+            c.m_blk = tile_m_blk(t);   // 128-row block index of this CTA's rows
             c.m0 = c.m_blk * BLOCK_M;
             const uint32_t buf = cc & 1;
-            typename Epi::Tile tile_state = Epi::begin_tile(ep, c);  // overlaps the wait below
+            c.dbg_tile = (int)cc;
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
+            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre);
+            if (t + num_pairs < num_tiles)
+                pre = Epi::preload(ep, c, tile_m_blk(t + num_pairs) * BLOCK_M, tile_n_blk(t + num_pairs) * 2);
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 2);
 #pragma unroll 1
             for (int nb = 0; nb < 2; ++nb) {   // the 256-wide tile as two 128-wide column blocks
                 c.n_blk = n_blk * 2 + nb;
@@ -272,7 +311,13 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
                 }
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 3 + 2 * nb);  // accumulator in registers
+#ifdef B200_EXP_NOEPI  // experiment: drain TMEM but skip the functor (keeps acc alive through a dummy store)
+                if (acc[0] == 12345.678f) reinterpret_cast<volatile float *>(epi_scratch)[lane] = acc[HN - 1];
+#else
                 Epi::template run<HN>(ep, c, tile_state, acc);
+#endif
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 4 + 2 * nb);  // run finished
             }
         }
     }
@@ -280,6 +325,246 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     tcgen05_fence_before();
     __syncthreads();
     cluster_sync_all();  // nobody may still be signalling into, or reading from, the peer
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// A-stationary variant for short reductions (Kd <= 512: the similarity GEMMs, Kd = D).
+//
+// The streaming kernel above is bound by operand delivery, not by the tensor cores: a 256 x 256
+// pair tile pulls 64 B/clk/SM of A and B from L2 at full MMA rate and the chip delivers ~44
+// (timeline of the instrumented build: MMA issue->commit 5100-6400 cycles per tile against 4096
+// at peak).  Here a pair keeps its 256 rows of A (all of K, 128 KB per SM) resident in shared
+// memory and walks the n-tiles of that row block, so only B streams through the ring: 32 B/clk/SM.
+// Tiles are taken in n-fastest order, one contiguous range per pair; A is reloaded when the range
+// crosses into the next row block (at most a few times per CTA).
+// ----------------------------------------------------------------------------------------------
+constexpr int ASTAT_MAX_K_ITERS = 8;
+
+template <int EPI_STAGE_BYTES>
+struct SmemLayoutAS {
+    static constexpr int A_KB_BYTES = BLOCK_M * BLOCK_K * 2;            // one k-block of this CTA's A rows
+    static constexpr int A_RES_BYTES = ASTAT_MAX_K_ITERS * A_KB_BYTES;  // 128 KB
+    static constexpr int B_BYTES = (PAIR_N / 2) * BLOCK_K * 2;          // this CTA's half of a B k-block
+    static constexpr int TAIL_BYTES = 8192;
+    static constexpr int MAX_SMEM = 232448;
+    static constexpr int STAGES_FIT = (MAX_SMEM - 1024 - TAIL_BYTES - EPI_STAGE_BYTES - A_RES_BYTES) / B_BYTES;
+    static constexpr int STAGES = STAGES_FIT > 6 ? 6 : STAGES_FIT;
+    static constexpr int TOTAL = A_RES_BYTES + STAGES * B_BYTES + EPI_STAGE_BYTES + TAIL_BYTES + 1024;
+    static_assert(STAGES >= 3, "pipeline too shallow");
+};
+
+template <class Epi>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(num_threads<Epi>(), 1)
+gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                          const GemmShape shape, const typename Epi::Params ep) {
+    using L = SmemLayoutAS<Epi::STAGE_BYTES>;
+    constexpr int STAGES = L::STAGES;
+    constexpr int HN = 128 / Epi::PARTS;
+    constexpr int NUM_EPI_WARPS = 4 * Epi::PARTS;
+    constexpr uint32_t TMEM_COLS = 512;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                ~(uintptr_t)1023);
+    uint8_t *a_res = smem;
+    uint8_t *ring = a_res + L::A_RES_BYTES;
+    uint8_t *epi_stage = ring + STAGES * L::B_BYTES;
+    uint8_t *tail = epi_stage + Epi::STAGE_BYTES;
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(tail);
+    uint64_t *empty_bar = full_bar + STAGES;
+    uint64_t *tfull_bar = empty_bar + STAGES;
+    uint64_t *tempty_bar = tfull_bar + 2;
+    uint64_t *afull_bar = tempty_bar + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(afull_bar + 2);  // (+2: keeps epi_scratch 16-byte aligned)
+    float *epi_scratch = reinterpret_cast<float *>(tmem_slot + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();  // 0 = leader
+    const int pair = blockIdx.x >> 1;
+    const int num_pairs = gridDim.x >> 1;
+
+    const int num_m = (shape.M + PAIR_M - 1) / PAIR_M;
+    const int num_n = (shape.N + PAIR_N - 1) / PAIR_N;
+    const int num_tiles = num_m * num_n;
+    const int k_iters = (shape.Kd + BLOCK_K - 1) / BLOCK_K;  // <= ASTAT_MAX_K_ITERS (host checks)
+    // this pair's contiguous range of the n-fastest tile order
+    const int t_begin = (int)((long long)pair * num_tiles / num_pairs);
+    const int t_end = (int)((long long)(pair + 1) * num_tiles / num_pairs);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_a);
+        tma_prefetch_desc(&map_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 2);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], 2 * NUM_EPI_WARPS);
+        }
+        mbar_init(afull_bar, 2);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_2sm(tmem_slot, TMEM_COLS);
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_trigger();
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int cur_m = -1, last_stage = -1;
+            uint32_t last_phase = 0;
+            for (int t = t_begin; t < t_end; ++t) {
+                const int m_blk = t / num_n, n_blk = t - m_blk * num_n;
+                if (m_blk != cur_m) {
+                    // the MMAs that read the previous row block are retired once the ring slot of
+                    // the last k-block issued so far has been released (commits complete in order)
+                    if (last_stage >= 0) mbar_wait(&empty_bar[last_stage], last_phase);
+                    const uint32_t lead_afull = mapa_u32(smem_u32(afull_bar), 0);
+                    mbar_expect_tx_cluster(lead_afull, (uint32_t)(k_iters * L::A_KB_BYTES));
+                    const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;
+                    for (int kb = 0; kb < k_iters; ++kb)
+                        tma_load_2d_2sm(a_res + kb * L::A_KB_BYTES, &map_a, lead_afull, kb * BLOCK_K, m0);
+                    cur_m = m_blk;
+                }
+                const int n0 = n_blk * PAIR_N + (int)rank * (PAIR_N / 2);
+                for (int kb = 0; kb < k_iters; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
+                    mbar_expect_tx_cluster(lead_full, L::B_BYTES);
+                    tma_load_2d_2sm(ring + stage * L::B_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                    last_stage = stage;
+                    last_phase = phase;
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA; convergent warp, one lane issues) =====
+        if (rank == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            uint32_t cc = 0, a_gen = 0;
+            int cur_m = -1;
+            const uint32_t sa_res = smem_u32(a_res), sb_ring = smem_u32(ring);
+            for (int t = t_begin; t < t_end; ++t, ++cc) {
+                const int m_blk = t / num_n;
+                const uint32_t buf = cc & 1;
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
+                mbar_wait_warp(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
+                if (m_blk != cur_m) {
+                    mbar_wait_warp(afull_bar, a_gen & 1);
+                    ++a_gen;
+                    cur_m = m_blk;
+                }
+                tcgen05_fence_after();
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
+                const uint32_t tmem_d = tmem_base + buf * PAIR_N;
+                for (int kb = 0; kb < k_iters; ++kb) {
+                    mbar_wait_warp(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t a_lo = smem_desc_lo(sa_res + (uint32_t)(kb * L::A_KB_BYTES));
+                    const uint32_t b_lo = smem_desc_lo(sb_ring + (uint32_t)(stage * L::B_BYTES));
+                    if (elect_one()) {
+                        umma_f16_2sm_lo(tmem_d, a_lo, b_lo, idesc, (uint32_t)(kb != 0));
+#pragma unroll
+                        for (int k = 1; k < BLOCK_K / UMMA_K; ++k)
+                            umma_f16_2sm_lo(tmem_d, a_lo + k * 2, b_lo + k * 2, idesc, 1u);
+                        umma_commit_2sm(&empty_bar[stage]);
+                    }
+                    __syncwarp();
+                    if (++stage == STAGES) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                if (elect_one()) umma_commit_2sm(&tfull_bar[buf]);
+                __syncwarp();
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 2);
+            }
+        }
+    } else {
+        // ===================== epilogue warps (both CTAs) =====================
+        EpiCtx c;
+        c.q = warp & 3;
+        c.half = (warp - 2) >> 2;
+        c.warp_slot = warp - 2;
+        c.lane = lane;
+        c.M = shape.M;
+        c.N = shape.N;
+        c.tid = c.q * 32 + lane;
+        c.etid = (warp - 2) * 32 + lane;
+        c.scratch = epi_scratch;
+        c.stage = epi_stage;
+        c.nthreads = NUM_EPI_WARPS * 32;
+        c.nsub = 2;
+        uint32_t cc = 0;
+        int runs = 0;
+        auto tile_m_blk = [&](int t) { return (t / num_n) * 2 + (int)rank; };
+        auto tile_n_blk = [&](int t) { return t % num_n; };
+        typename Epi::Pre pre{};
+        if (t_begin < t_end) pre = Epi::preload(ep, c, tile_m_blk(t_begin) * BLOCK_M, tile_n_blk(t_begin) * 2);
+        for (int t = t_begin; t < t_end; ++t, ++cc) {
+            const int n_blk = tile_n_blk(t);
+            c.m_blk = tile_m_blk(t);
+            c.m0 = c.m_blk * BLOCK_M;
+            const uint32_t buf = cc & 1;
+            c.dbg_tile = (int)cc;
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
+            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre);
+            if (t + 1 < t_end) pre = Epi::preload(ep, c, tile_m_blk(t + 1) * BLOCK_M, tile_n_blk(t + 1) * 2);
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
+            mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
+            tcgen05_fence_after();
+            epi_stamp(Epi::STAMP_KIND, (int)cc, 2);
+#pragma unroll 1
+            for (int nb = 0; nb < 2; ++nb) {
+                c.n_blk = n_blk * 2 + nb;
+                c.sub = nb;
+                c.n0 = c.n_blk * 128 + c.half * HN;
+                c.par = runs & 1;
+                ++runs;
+                const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * PAIR_N +
+                                       (uint32_t)(nb * 128 + c.half * HN);
+                float acc[HN];
+#pragma unroll
+                for (int ch = 0; ch < HN / 32; ++ch) {
+                    float v[32];
+                    tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) acc[ch * 32 + i] = v[i];
+                }
+                if (nb == 1) {
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
+                }
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 3 + 2 * nb);
+                Epi::template run<HN>(ep, c, tile_state, acc);
+                epi_stamp(Epi::STAMP_KIND, (int)cc, 4 + 2 * nb);
+            }
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();
     if (warp == 1) {
         tcgen05_fence_after();
         tmem_dealloc_2sm(tmem_base, TMEM_COLS);

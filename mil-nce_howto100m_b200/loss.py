@@ -50,8 +50,8 @@ class CudaBackend:
         return loss, den, nom, ws
 
     @staticmethod
-    def backward(video, text, den, nom, grad_loss, i0, n, ws):
-        """Returns float32 (dvideo (n, D), dtext (n*K, D)): the rows this range owns."""
+    def backward(video, text, den, nom, grad_loss, i0, n, ws, grad_dtype=torch.float32):
+        """Returns (dvideo (n, D), dtext (n*K, D)) in grad_dtype: the rows this range owns."""
         lib = _lib.load()
         B, D = video.shape
         K = text.shape[0] // B
@@ -62,11 +62,14 @@ class CudaBackend:
             nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
             ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
             reuse = 0
-        dv = torch.empty(n, D, dtype=torch.float32, device=dev)
-        dt = torch.empty(n * K, D, dtype=torch.float32, device=dev)
+        if grad_dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("grad_dtype must be float32 or bfloat16")
+        dv = torch.empty(n, D, dtype=grad_dtype, device=dev)
+        dt = torch.empty(n * K, D, dtype=grad_dtype, device=dev)
+        gcode = 0 if grad_dtype == torch.float32 else 1
         with torch.cuda.device(dev):
             rc = lib.milnce_backward(_ptr(video), _ptr(text), _ptr(den), _ptr(nom), _ptr(grad_loss),
-                                     _ptr(dv), _ptr(dt), B, K, D, code, i0, n, reuse, _ptr(ws),
+                                     _ptr(dv), _ptr(dt), gcode, B, K, D, code, i0, n, reuse, _ptr(ws),
                                      ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "milnce_backward")
         return dv, dt
@@ -152,9 +155,10 @@ class _MILNCEFunction(torch.autograd.Function):
     def backward(ctx, grad_output):
         v, t, den, nom = ctx.saved_tensors
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
-        dv, dt = CudaBackend.backward(v, t, den, nom, g, 0, v.shape[0], ctx.ws)
+        # gradients come back in the input dtype straight from the GEMM epilogues
+        dv, dt = CudaBackend.backward(v, t, den, nom, g, 0, v.shape[0], ctx.ws, grad_dtype=v.dtype)
         ctx.ws = None
-        return dv.to(v.dtype), dt.to(t.dtype)
+        return dv, dt
 
 
 class MILNCELoss(torch.nn.Module):
