@@ -102,7 +102,7 @@ namespace b200 {
 bool pdl_enabled() {
     static const bool v = [] {
         const char *e = getenv("B200HEAD_PDL");
-        return !(e && e[0] == '0');
+        return e && e[0] == '1';  // opt-in: measured neutral on the benchmark shape (0.993 vs 0.997 ms)
     }();
     return v;
 }

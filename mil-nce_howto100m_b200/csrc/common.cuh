@@ -30,8 +30,8 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // kernel of the stream is still draining, so its prologue (barrier set-up, TMEM allocation,
 // descriptor prefetch) and the launch latency overlap that kernel's tail.  Every kernel launched
 // this way executes griddepcontrol.wait (tc::pdl_wait) before it touches global memory, which
-// blocks until the previous grid has completed and its writes are visible.  B200HEAD_PDL=0 in the
-// environment falls back to plain launches (for A/B timing).
+// blocks until the previous grid has completed and its writes are visible.  Off unless B200HEAD_PDL=1
+// is set in the environment: it measured neutral on the benchmark shape, plain launches are the default.
 bool pdl_enabled();
 template <class... KArgs, class... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,

@@ -588,7 +588,9 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     tc::GemmShape shape{M, N, Kd, 0};
     (void)what;
     // short reductions with an epilogue-heavy functor: keep A resident, stream only B
-    constexpr bool CAN_ASTAT = !A_MN && !std::is_same<Epi, tc::EpiStore>::value;
+    // (not for EpiG: its 32 KB store-staging buffer leaves only three ring stages next to the resident A,
+    // measured slower)
+    constexpr bool CAN_ASTAT = !A_MN && Epi::STAGE_BYTES == 0 && !std::is_same<Epi, tc::EpiStore>::value;
     if constexpr (CAN_ASTAT) {
         if (Kd <= tc::ASTAT_MAX_K_ITERS * tc::BLOCK_K && astat_enabled()) {
             using LA = tc::SmemLayoutAS<Epi::STAGE_BYTES>;
@@ -772,7 +774,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
     rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
-                                                            "milnce dvideo GEMM")
+                                            "milnce dvideo GEMM")
                     : launch_gemm<tc::EpiStore, false, 1, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D,
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
@@ -794,7 +796,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
             ld_g2 = p.ld_g2;
         }
         rc = launch_gemm2<tc::EpiStore, true, true>(g2, ld_g2, vt, p.ld_vt, p.n * p.K, p.D, p.B, sd, st,
-                                                    "milnce dtext GEMM (MN-major G)");
+                                    "milnce dtext GEMM (MN-major G)");
         return rc;
     }
     // fp32 inputs (hi/lo planes): the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
@@ -861,12 +863,12 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     if (rc) return rc;
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
     rc = launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
-                                                 "milnce dvideo GEMM (shard)");
+                                            "milnce dvideo GEMM (shard)");
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
     tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext, 0};
-    return launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd,
-                                                  st, "milnce partial dtext GEMM (shard)");
+    return launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd, st,
+                                "milnce partial dtext GEMM (shard)");
 }
 
 int check_shard(const Plan &p, int dtype) {

@@ -270,6 +270,16 @@ inline FastDiv make_fastdiv(int d) {
     return f;
 }
 
+// A load the compiler must leave where it is written (asm volatile keeps its order relative to the
+// other volatile statements - TMEM loads, barrier waits): used to issue per-tile lookups one tile
+// ahead.  A plain __ldg is sunk down to its first use under register pressure, which puts the whole
+// L2 round trip back on the critical path.
+__device__ __forceinline__ float ldg_pinned(const float *p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
 // explicit shared-space accesses: pointers that travel through EpiCtx are generic to the
 // compiler, which then emits generic LD/ST for them
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4 &v) {
@@ -343,11 +353,20 @@ struct EpiStore {
         float alpha;
     };
     struct Pre {};
+    struct Consts {
+        float alpha;
+    };
+    // kernel-lifetime scalars, loaded once per thread before the tile loop
+    __device__ static Consts load_consts(const Params &p) {
+        Consts k;
+        k.alpha = p.alpha;
+        if (p.alpha_dev) k.alpha *= __ldg(p.alpha_dev);
+        return k;
+    }
     __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &, const Pre &) {
+    __device__ static Tile begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k) {
         Tile t;
-        t.alpha = p.alpha;
-        if (p.alpha_dev) t.alpha *= __ldg(p.alpha_dev);
+        t.alpha = k.alpha;
         return t;
     }
     template <int HN>
@@ -470,10 +489,18 @@ struct EpiRowColT {
         float row_m, row_s;  // row statistic carried across the column sub-blocks of one tile: 2^row_m * row_s
     };
     struct Pre {};
+    struct Consts {
+        float sc;
+    };
+    __device__ static Consts load_consts(const Params &p) {
+        Consts k;
+        k.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        return k;
+    }
     __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &, const Pre &) {
+    __device__ static Tile begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k) {
         Tile t;
-        t.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        t.sc = k.sc;
         t.row_m = -INFINITY;
         t.row_s = 0.f;
         return t;
@@ -627,7 +654,10 @@ struct GFast {
 struct EpiG {
     static constexpr int STAMP_KIND = 2;
     static constexpr int STAGE_BYTES = 4 * 32 * 128 * 2;  // 32 KB: a 128 x 128 fp16 block
-    static constexpr int PARTS = 4;
+#ifndef B200_EPIG_PARTS
+#define B200_EPIG_PARTS 4
+#endif
+    static constexpr int PARTS = B200_EPIG_PARTS;
     struct Params {
         const float *den;  // all B entries
         const float *nom;
@@ -715,22 +745,35 @@ struct EpiG {
     __device__ static Pre preload(const Params &p, const EpiCtx &c, int m0, int n_blk0) {
         Pre q;
         const int HN = 128 / PARTS;
-        q.den_r = __ldg(p.den + p.rdiv.div(p.row_off + min(m0 + c.tid, c.M - 1)));
+        q.den_r = ldg_pinned(p.den + p.rdiv.div(p.row_off + min(m0 + c.tid, c.M - 1)));
 #pragma unroll
         for (int s = 0; s < 2; ++s)
 #pragma unroll
             for (int h = 0; h < HN / 32; ++h) {
                 const int n = (n_blk0 + s) * 128 + c.half * HN + h * 32 + c.lane;
                 q.den_c[s * (HN / 32) + h] =
-                    (s < c.nsub && n < c.N) ? __ldg(p.den + p.cdiv.div(p.col_off + n)) : INFINITY;
+                    (s < c.nsub && n < c.N) ? ldg_pinned(p.den + p.cdiv.div(p.col_off + n)) : INFINITY;
             }
         return q;
     }
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c, const Pre &q) {
+    // (loading these three at every tile start exposed an L2 round trip per tile: ~1000 cycles
+    // between a warp's last run and its next wait in the instrumented timeline)
+    struct Consts {
+        bool fast;
+        float mid, sc;
+    };
+    __device__ static Consts load_consts(const Params &p) {
+        Consts k;
+        k.fast = __ldg(p.fast.flag_dev) != 0;
+        k.mid = __ldg(p.fast.mid_log2_dev);
+        k.sc = __ldg(p.scale_dev) * LOG2E;
+        return k;
+    }
+    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c, const Pre &q, const Consts &k) {
         Tile t;
-        t.fast = __ldg(p.fast.flag_dev) != 0;
-        t.mid = __ldg(p.fast.mid_log2_dev);
-        t.sc = __ldg(p.scale_dev) * LOG2E;
+        t.fast = k.fast;
+        t.mid = k.mid;
+        t.sc = k.sc;
         const float dr = q.den_r * LOG2E;
         t.dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
         t.ar = t.fast ? fast_exp2(dr - t.mid) : 0.f;
@@ -1063,7 +1106,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
                 }
-                typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk));
+                typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk), Epi::load_consts(ep));
                 Epi::template run<HN>(ep, c, tile_state, acc);
             } else {
                 // two row blocks, one chunk: drain and process them one after the other
@@ -1091,7 +1134,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // both row blocks drained
                     }
-                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk));
+                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk), Epi::load_consts(ep));
                     Epi::template run<HN>(ep, c, tile_state, acc);
                 }
                 ++cc;

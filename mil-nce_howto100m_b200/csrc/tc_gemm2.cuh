@@ -177,8 +177,8 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     pdl_trigger();  // the next kernel may be scheduled onto SMs as this grid's CTAs retire
 
     if (warp == 0) {
-        // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
+        // ===================== TMA producer (both CTAs; convergent warp, one lane issues) =====
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int t = pair; t < num_tiles; t += num_pairs) {
@@ -187,25 +187,24 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;        // my rows of A
                 const int n0 = n_blk * PAIR_N + (int)rank * (PAIR_N / 2);   // my half of B
                 for (int kb = 0; kb < k_iters; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
+                    mbar_wait_warp(&empty_bar[stage], phase ^ 1);
+                    if (elect_one()) {
+                        const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
 #ifdef B200_EXP_NOTMA  // experiment: no operand traffic at all (results are garbage, timing only)
-                    mbar_arrive_cluster(lead_full);
-                    if (++stage == STAGES) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
-                    continue;
+                        mbar_arrive_cluster(lead_full);
+#else
+                        mbar_expect_tx_cluster(lead_full, L::STAGE_BYTES);
+                        uint8_t *sa = smem + stage * L::STAGE_BYTES;
+                        if (A_MN) {
+                            tma_load_2d_2sm(sa, &map_a, lead_full, m0, kb * BLOCK_K);
+                            tma_load_2d_2sm(sa + L::A_BYTES / 2, &map_a, lead_full, m0 + 64, kb * BLOCK_K);
+                        } else {
+                            tma_load_2d_2sm(sa, &map_a, lead_full, kb * BLOCK_K, m0);
+                        }
+                        tma_load_2d_2sm(sa + L::A_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
 #endif
-                    mbar_expect_tx_cluster(lead_full, L::STAGE_BYTES);
-                    uint8_t *sa = smem + stage * L::STAGE_BYTES;
-                    if (A_MN) {
-                        tma_load_2d_2sm(sa, &map_a, lead_full, m0, kb * BLOCK_K);
-                        tma_load_2d_2sm(sa + L::A_BYTES / 2, &map_a, lead_full, m0 + 64, kb * BLOCK_K);
-                    } else {
-                        tma_load_2d_2sm(sa, &map_a, lead_full, kb * BLOCK_K, m0);
                     }
-                    tma_load_2d_2sm(sa + L::A_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -270,21 +269,37 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         c.nsub = 2;
         uint32_t cc = 0;
         int runs = 0;
-        auto tile_m_blk = [&](int t) { return (N_FAST ? t / num_n : t % num_m) * 2 + (int)rank; };
-        auto tile_n_blk = [&](int t) { return N_FAST ? t % num_n : t / num_m; };
+        // tile coordinates advance incrementally (no integer division per tile): (fast, slow) are
+        // (n, m) in n-fastest order and (m, n) otherwise
+        const int fast_n = N_FAST ? num_n : num_m;
+        int cur_fast = pair % fast_n, cur_slow = pair / fast_n;
+        const int step_fast = num_pairs % fast_n, step_slow = num_pairs / fast_n;
+        auto advance = [&](int &f, int &sl) {
+            f += step_fast;
+            sl += step_slow;
+            if (f >= fast_n) {
+                f -= fast_n;
+                ++sl;
+            }
+        };
         // per-sample values of a tile are loaded one tile ahead (Epi::preload), see EpiG
+        const typename Epi::Consts consts = Epi::load_consts(ep);
         typename Epi::Pre pre{};
-        if (pair < num_tiles) pre = Epi::preload(ep, c, tile_m_blk(pair) * BLOCK_M, tile_n_blk(pair) * 2);
+        if (pair < num_tiles)
+            pre = Epi::preload(ep, c, ((N_FAST ? cur_slow : cur_fast) * 2 + (int)rank) * BLOCK_M,
+                               (N_FAST ? cur_fast : cur_slow) * 2);
         for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
-            const int n_blk = tile_n_blk(t);
-            c.m_blk = tile_m_blk(t);   // 128-row block index of this CTA's rows
+            const int n_blk = N_FAST ? cur_fast : cur_slow;
+            c.m_blk = (N_FAST ? cur_slow : cur_fast) * 2 + (int)rank;   // 128-row block index of this CTA's rows
             c.m0 = c.m_blk * BLOCK_M;
+            advance(cur_fast, cur_slow);  // now the coordinates of tile t + num_pairs
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
             epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
-            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre);
+            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre, consts);
             if (t + num_pairs < num_tiles)
-                pre = Epi::preload(ep, c, tile_m_blk(t + num_pairs) * BLOCK_M, tile_n_blk(t + num_pairs) * 2);
+                pre = Epi::preload(ep, c, ((N_FAST ? cur_slow : cur_fast) * 2 + (int)rank) * BLOCK_M,
+                                   (N_FAST ? cur_fast : cur_slow) * 2);
             epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
@@ -420,8 +435,8 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     pdl_trigger();
 
     if (warp == 0) {
-        // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
+        // ===================== TMA producer (both CTAs; convergent warp, one lane issues) =====
+        {
             int stage = 0;
             uint32_t phase = 0;
             int cur_m = -1, last_stage = -1;
@@ -431,20 +446,26 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
                 if (m_blk != cur_m) {
                     // the MMAs that read the previous row block are retired once the ring slot of
                     // the last k-block issued so far has been released (commits complete in order)
-                    if (last_stage >= 0) mbar_wait(&empty_bar[last_stage], last_phase);
-                    const uint32_t lead_afull = mapa_u32(smem_u32(afull_bar), 0);
-                    mbar_expect_tx_cluster(lead_afull, (uint32_t)(k_iters * L::A_KB_BYTES));
-                    const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;
-                    for (int kb = 0; kb < k_iters; ++kb)
-                        tma_load_2d_2sm(a_res + kb * L::A_KB_BYTES, &map_a, lead_afull, kb * BLOCK_K, m0);
+                    if (last_stage >= 0) mbar_wait_warp(&empty_bar[last_stage], last_phase);
+                    if (elect_one()) {
+                        const uint32_t lead_afull = mapa_u32(smem_u32(afull_bar), 0);
+                        mbar_expect_tx_cluster(lead_afull, (uint32_t)(k_iters * L::A_KB_BYTES));
+                        const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;
+                        for (int kb = 0; kb < k_iters; ++kb)
+                            tma_load_2d_2sm(a_res + kb * L::A_KB_BYTES, &map_a, lead_afull, kb * BLOCK_K, m0);
+                    }
+                    __syncwarp();
                     cur_m = m_blk;
                 }
                 const int n0 = n_blk * PAIR_N + (int)rank * (PAIR_N / 2);
                 for (int kb = 0; kb < k_iters; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
-                    mbar_expect_tx_cluster(lead_full, L::B_BYTES);
-                    tma_load_2d_2sm(ring + stage * L::B_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                    mbar_wait_warp(&empty_bar[stage], phase ^ 1);
+                    if (elect_one()) {
+                        const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
+                        mbar_expect_tx_cluster(lead_full, L::B_BYTES);
+                        tma_load_2d_2sm(ring + stage * L::B_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                    }
+                    __syncwarp();
                     last_stage = stage;
                     last_phase = phase;
                     if (++stage == STAGES) {
@@ -518,6 +539,7 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         int runs = 0;
         auto tile_m_blk = [&](int t) { return (t / num_n) * 2 + (int)rank; };
         auto tile_n_blk = [&](int t) { return t % num_n; };
+        const typename Epi::Consts consts = Epi::load_consts(ep);
         typename Epi::Pre pre{};
         if (t_begin < t_end) pre = Epi::preload(ep, c, tile_m_blk(t_begin) * BLOCK_M, tile_n_blk(t_begin) * 2);
         for (int t = t_begin; t < t_end; ++t, ++cc) {
@@ -527,7 +549,7 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
             epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
-            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre);
+            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre, consts);
             if (t + 1 < t_end) pre = Epi::preload(ep, c, tile_m_blk(t + 1) * BLOCK_M, tile_n_blk(t + 1) * 2);
             epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
