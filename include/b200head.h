@@ -91,15 +91,26 @@ int milnce_backward(const void *video, const void *text, const float *den, const
  *             nom[i0, i0+n)      as in milnce_forward
  *             The caller all-gathers row_lse / nom, logsumexp-reduces col_part over ranks and forms
  *             den_j = logaddexp(row_lse_j, col_j), loss = mean(den - nom).
- *   backward: dvideo (n, D) complete for the owned rows; dtext_partial (B*K, D) float32 holds only
- *             the owned rows' contribution: reduce-scatter (sum) it over ranks to obtain each
- *             rank's (n*K, D) slice. */
+ *   backward: dvideo (n, D) complete for the owned rows, written as dvideo_dtype (F32 or BF16);
+ *             dtext_partial (B*K, D) float32 holds only the owned rows' contribution:
+ *             reduce-scatter (sum) it over ranks to obtain each rank's (n*K, D) slice.
+ *             parts = 3 computes both.  parts = 1 computes the gradient tile matrix and
+ *             dtext_partial only (dvideo may be NULL); a following parts = 2 call with the same
+ *             workspace computes dvideo (dtext_partial may be NULL), so the reduce-scatter of
+ *             dtext can run while dvideo is computed. */
 int milnce_forward_shard(const void *video, const void *text, int B, int K, int D, int dtype,
                          int i0, int n, float *row_lse, float *col_part, float *nom,
                          void *workspace, size_t workspace_bytes, void *stream);
+/* After the exchange of the rows-only scheme: `gathered` is (W, 2b + B) float32, rank r's row =
+ * [row_lse of its b samples | nom of its b samples | its col_part of all B = W*b samples] (the
+ * all-gather of what milnce_forward_shard produced).  Writes den[B], nom[B] and loss[0] =
+ * mean(den - nom); identical on every rank.  (The reference has no counterpart: there the full
+ * similarity matrix is reduced on every rank, loss.py:16-18.) */
+int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom, float *loss,
+                         void *stream);
 int milnce_backward_shard(const void *video, const void *text, const float *den, const float *nom,
-                          const float *grad_loss, float *dvideo, float *dtext_partial,
-                          int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
+                          const float *grad_loss, void *dvideo, int dvideo_dtype, float *dtext_partial,
+                          int parts, int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
                           void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------

@@ -72,8 +72,10 @@ def _declare(lib):
                                     vp, sz, vp]
     lib.milnce_forward_shard.restype = i32
     lib.milnce_forward_shard.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, fp, fp, fp, vp, sz, vp]
+    lib.milnce_shard_combine.restype = i32
+    lib.milnce_shard_combine.argtypes = [fp, i32, i32, fp, fp, fp, vp]
     lib.milnce_backward_shard.restype = i32
-    lib.milnce_backward_shard.argtypes = [vp, vp, fp, fp, fp, fp, fp, i32, i32, i32, i32, i32, i32, i32,
+    lib.milnce_backward_shard.argtypes = [vp, vp, fp, fp, fp, vp, i32, fp, i32, i32, i32, i32, i32, i32, i32, i32,
                                           vp, sz, vp]
     lib.sdtw_aux_bytes.restype = sz
     lib.sdtw_aux_bytes.argtypes = [i32, i32, i32, i32]

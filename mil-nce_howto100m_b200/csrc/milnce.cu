@@ -523,6 +523,42 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
     if (lane == 0) nom[i] = pm + logf(ps);
 }
 
+// Rows-only sharding, after the exchange: allp is (W, 2b + B) = per rank [row_lse of its b samples |
+// nom of its b samples | its partial column statistic of all B samples].  One block:
+//   den_j = logaddexp(row_j, logsumexp_r col_part[r][j]), nom_all, loss = mean(den - nom)
+// (replaces a cat / logsumexp / logaddexp / mean chain of eight small torch launches).
+__global__ void __launch_bounds__(1024)
+shard_combine_kernel(const float *__restrict__ allp, int W, int b, int B, float *__restrict__ den,
+                     float *__restrict__ nom_all, float *__restrict__ loss) {
+    __shared__ double sh[32];
+    const size_t ld = (size_t)2 * b + B;
+    double acc = 0.0;
+    for (int j = threadIdx.x; j < B; j += blockDim.x) {
+        const int r = j / b, i = j - r * b;
+        const float row = allp[(size_t)r * ld + i];
+        const float nm = allp[(size_t)r * ld + b + i];
+        float m = row;
+        for (int w = 0; w < W; ++w) m = fmaxf(m, allp[(size_t)w * ld + 2 * b + j]);
+        float sum = 0.f;
+        if (m > -INFINITY) {
+            sum = expf(row - m);
+            for (int w = 0; w < W; ++w) sum += expf(allp[(size_t)w * ld + 2 * b + j] - m);
+        }
+        const float d = m + logf(sum);
+        den[j] = d;
+        nom_all[j] = nm;
+        acc += (double)(d - nm);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        acc = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (threadIdx.x == 0) loss[0] = (float)(acc / (double)B);
+    }
+}
+
 // ----------------------------------------------------------------------------
 // host helpers
 // ----------------------------------------------------------------------------
@@ -841,34 +877,42 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
 }
 
 int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
-                        const float *den, const float *nom, const float *grad_loss, float *dvideo,
-                        float *dtext_partial, int reuse, uint8_t *ws, cudaStream_t st) {
-    const int grad_bf16 = 0;
+                        const float *den, const float *nom, const float *grad_loss, void *dvideo,
+                        int grad_bf16, float *dtext_partial, int parts, int reuse, uint8_t *ws,
+                        cudaStream_t st) {
+    // parts: 1 = G and the partial dtext, 2 = dvideo (from the G a parts-1 call left in the
+    // workspace), 3 = both.  Split calls let the caller start the reduce-scatter of dtext
+    // while dvideo is still being computed.
     int rc;
+    const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
+    __half *g = reinterpret_cast<__half *>(ws + p.off_g);
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    if (parts == 2) {
+        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
+        return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+                                                       "milnce dvideo GEMM (shard)");
+    }
     if (!reuse) {
         rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
         if (rc) return rc;
     }
-    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
-    const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
-    __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
     rc = launch_gemm2<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
                                 st, "milnce backward (rows-only shard) G");
     if (rc) return rc;
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
-    rc = launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
-                                            "milnce dvideo GEMM (shard)");
-    if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
     tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext, 0};
-    return launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd, st,
-                                "milnce partial dtext GEMM (shard)");
+    rc = launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd, st,
+                                                "milnce partial dtext GEMM (shard)");
+    if (rc || parts == 1) return rc;
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
+    return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+                                                   "milnce dvideo GEMM (shard)");
 }
 
 int check_shard(const Plan &p, int dtype) {
@@ -1022,17 +1066,35 @@ extern "C" int milnce_forward_shard(const void *video, const void *text, int B, 
                               col_part, nom, (uint8_t *)workspace, (cudaStream_t)stream);
 }
 
+extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom,
+                                    float *loss, void *stream) {
+    if (!gathered || !den || !nom || !loss || W <= 0 || b <= 0) {
+        b200::set_error("milnce_shard_combine: bad argument");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(gathered, W, b, W * b, den, nom, loss);
+    B200_LAUNCH_OK("milnce_shard_combine");
+    return 0;
+}
+
 extern "C" int milnce_backward_shard(const void *video, const void *text, const float *den,
-                                     const float *nom, const float *grad_loss, float *dvideo,
-                                     float *dtext_partial, int B, int K, int D, int dtype, int i0, int n,
-                                     int reuse_forward_ws, void *workspace, size_t workspace_bytes,
-                                     void *stream) {
+                                     const float *nom, const float *grad_loss, void *dvideo,
+                                     int dvideo_dtype, float *dtext_partial, int parts, int B, int K, int D,
+                                     int dtype, int i0, int n, int reuse_forward_ws, void *workspace,
+                                     size_t workspace_bytes, void *stream) {
     Plan p;
     if (!make_plan(p, B, K, D, dtype == B200HEAD_BF16 ? dtype : B200HEAD_BF16, i0, n)) {
         b200::set_error("milnce_backward_shard: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
         return B200HEAD_ERR_ARG;
     }
-    if (!video || !text || !den || !nom || !grad_loss || !dvideo || !dtext_partial) {
+    if (parts < 1 || parts > 3 || (dvideo_dtype != B200HEAD_F32 && dvideo_dtype != B200HEAD_BF16)) {
+        b200::set_error("milnce_backward_shard: parts must be 1, 2 or 3 and dvideo_dtype F32 or BF16");
+        return B200HEAD_ERR_ARG;
+    }
+    if (!video || !text || !den || !nom || !grad_loss || ((parts & 2) && !dvideo) ||
+        ((parts & 1) && !dtext_partial)) {
         b200::set_error("milnce_backward_shard: null pointer argument");
         return B200HEAD_ERR_ARG;
     }
@@ -1043,6 +1105,6 @@ extern "C" int milnce_backward_shard(const void *video, const void *text, const 
     rc = check_common(p, workspace, workspace_bytes);
     if (rc) return rc;
     return backward_shard_impl(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text, den, nom,
-                               grad_loss, dvideo, dtext_partial, reuse_forward_ws, (uint8_t *)workspace,
-                               (cudaStream_t)stream);
+                               grad_loss, dvideo, dvideo_dtype == B200HEAD_BF16 ? 1 : 0, dtext_partial, parts,
+                               reuse_forward_ws, (uint8_t *)workspace, (cudaStream_t)stream);
 }

@@ -100,8 +100,26 @@ class CudaBackend:
         return row, colp, nom, ws
 
     @staticmethod
-    def backward_shard(video, text, den, nom, grad_loss, i0, n, ws):
-        """Returns float32 (dvideo (n, D), dtext_partial (B*K, D)); the latter is to be reduce-scattered."""
+    def shard_combine(gathered, world, b):
+        """(den[B], nom[B], loss) from the all-gathered (W, 2b + B) statistics of forward_shard."""
+        lib = _lib.load()
+        dev = gathered.device
+        B = world * b
+        den = torch.empty(B, dtype=torch.float32, device=dev)
+        nom = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_shard_combine(_ptr(gathered), world, b, _ptr(den), _ptr(nom), _ptr(loss),
+                                          _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_shard_combine")
+        return den, nom, loss.reshape(())
+
+    @staticmethod
+    def backward_shard(video, text, den, nom, grad_loss, i0, n, ws, parts=3, grad_dtype=torch.float32):
+        """Returns (dvideo (n, D) in grad_dtype or None, dtext_partial (B*K, D) float32 or None).
+
+        parts=1: gradient tiles + dtext_partial only; parts=2: dvideo only, from the workspace a
+        parts=1 call left; parts=3: both.  dtext_partial is to be reduce-scattered."""
         lib = _lib.load()
         B, D = video.shape
         K = text.shape[0] // B
@@ -109,15 +127,21 @@ class CudaBackend:
         dev = video.device
         reuse = 1
         if ws is None:
+            if parts == 2:
+                raise ValueError("parts=2 needs the workspace of the parts=1 call")
             nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
             ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
             reuse = 0
-        dv = torch.empty(n, D, dtype=torch.float32, device=dev)
-        dtp = torch.empty(B * K, D, dtype=torch.float32, device=dev)
+        dv = torch.empty(n, D, dtype=grad_dtype, device=dev) if parts & 2 else None
+        dtp = torch.empty(B * K, D, dtype=torch.float32, device=dev) if parts & 1 else None
+        gcode = 0 if grad_dtype == torch.float32 else 1
+        null = ctypes.c_void_p(0)
         with torch.cuda.device(dev):
             rc = lib.milnce_backward_shard(_ptr(video), _ptr(text), _ptr(den), _ptr(nom), _ptr(grad_loss),
-                                           _ptr(dv), _ptr(dtp), B, K, D, code, i0, n, reuse, _ptr(ws),
-                                           ws.numel(), _lib.stream_ptr(dev))
+                                           _ptr(dv) if dv is not None else null, gcode,
+                                           _ptr(dtp) if dtp is not None else null, parts,
+                                           B, K, D, code, i0, n, reuse, _ptr(ws), ws.numel(),
+                                           _lib.stream_ptr(dev))
         _lib.check(rc, "milnce_backward_shard")
         return dv, dtp
 

@@ -116,12 +116,7 @@ class _GatheredMILNCERows(torch.autograd.Function):
         pack = torch.cat([row[i0:i0 + b], nom[i0:i0 + b], colp]).contiguous()
         allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
         dist.all_gather_into_tensor(allp, pack, group=group)
-        allp = allp.view(world, 2 * b + B)
-        row_all = allp[:, :b].reshape(B)
-        nom_all = allp[:, b:2 * b].reshape(B).contiguous()
-        col_all = torch.logsumexp(allp[:, 2 * b:], dim=0)
-        den = torch.logaddexp(row_all, col_all).contiguous()
-        loss = (den - nom_all).mean()
+        den, nom_all, loss = backend.shard_combine(allp.view(world, 2 * b + B), world, b)
         ctx.save_for_backward(V, T, den, nom_all)
         ctx.ws = ws
         ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0])
@@ -132,11 +127,14 @@ class _GatheredMILNCERows(torch.autograd.Function):
         V, T, den, nom = ctx.saved_tensors
         i0, b, backend, vdt, tdt, group, bk_local = ctx.meta
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
-        dv, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws)
-        ctx.ws = None
+        # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
+        _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1)
         dt = torch.empty((bk_local, dt_partial.shape[1]), dtype=dt_partial.dtype, device=dt_partial.device)
-        dist.reduce_scatter_tensor(dt, dt_partial, op=dist.ReduceOp.SUM, group=group)
-        return dv.to(vdt), dt.to(tdt), None, None, None, None
+        work = dist.reduce_scatter_tensor(dt, dt_partial, op=dist.ReduceOp.SUM, group=group, async_op=True)
+        dv, _ = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=2, grad_dtype=vdt)
+        ctx.ws = None
+        work.wait()
+        return dv, dt.to(tdt), None, None, None, None
 
 
 class GatheredMILNCELoss(torch.nn.Module):

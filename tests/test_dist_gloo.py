@@ -83,7 +83,16 @@ class OracleBackend:
         return torch.from_numpy(row), torch.from_numpy(colp), torch.from_numpy(nm), None
 
     @staticmethod
-    def backward_shard(V, T, den, nom, g, i0, n, ws):
+    def shard_combine(allp, world, b):
+        B = world * b
+        row_all = allp[:, :b].reshape(B)
+        nom_all = allp[:, b:2 * b].reshape(B).contiguous()
+        col_all = torch.logsumexp(allp[:, 2 * b:], dim=0)
+        den = torch.logaddexp(row_all, col_all).contiguous()
+        return den, nom_all, (den - nom_all).mean()
+
+    @staticmethod
+    def backward_shard(V, T, den, nom, g, i0, n, ws, parts=3, grad_dtype=None):
         v = V.double().numpy()
         t = T.double().numpy()
         B = v.shape[0]
@@ -97,7 +106,9 @@ class OracleBackend:
         for r in range(n):
             g_r[r, i0 + r, :] -= np.exp(x[i0 + r, i0 + r, :] - nom[i0 + r])
         g_r = (float(g[0]) / B) * g_r.reshape(n, B * K)
-        return torch.from_numpy(g_r @ t), torch.from_numpy(g_r.T @ v[rows])
+        dv = torch.from_numpy(g_r @ t) if parts & 2 else None
+        dtp = torch.from_numpy(g_r.T @ v[rows]) if parts & 1 else None
+        return dv, dtp
 
 
 def _free_port():
