@@ -170,6 +170,15 @@ def run_reference(args):
 # ----------------------------------------------------------------------------
 # our arm
 # ----------------------------------------------------------------------------
+def measured_traffic():
+    """DRAM bytes per step from the committed ncu --set full captures (profiles/r1_traffic.json)."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
 def timed(fn, steps, warmup, barrier):
     for _ in range(warmup):
         fn()
@@ -310,8 +319,10 @@ def run_b200(args):
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": None,
-                     "note": f"algorithmic 6*B*BK*D FLOP per step / step time; peak = bf16 sustained, {pk['src']}"},
+                     "frac": achieved / peak,
+                     "traffic": measured_traffic().get("milnce_step_dram_bytes") if (B, K, D, args.dtype) == (8192, 4, 512, "bf16") else None,
+                     "note": (f"algorithmic 6*B*BK*D FLOP per step / step time; peak = bf16 sustained, {pk['src']}; "
+                              "traffic = DRAM bytes of one step's four GEMM kernels (ncu --set full, profiles/r1_traffic.json)")},
     }
     if rank == 0:
         line["clocks"] = clk.summary()
@@ -360,7 +371,8 @@ def bench_sdtw(dev, pk, args):
            "ms_per_step": ms, "config": {"workload": "SoftDTW(gamma=0.1, cosine) fwd+bwd 256x(64x64)x512 fp32",
                                          "l2": "4 rotating input sets (268 MB) exceed L2"},
            "roofline": {"bound": "hbm", "achieved": alg_bytes / (ms * 1e-3) / 1e9, "peak": pk["hbm"],
-                        "unit": "GB/s", "frac": alg_bytes / (ms * 1e-3) / 1e9 / pk["hbm"], "traffic": None}}
+                        "unit": "GB/s", "frac": alg_bytes / (ms * 1e-3) / 1e9 / pk["hbm"],
+                        "traffic": measured_traffic().get("sdtw_step_dram_bytes")}}
     if not args.no_cpu:
         val, s = cpu_sdtw(16, N, M, d)
         out["cpu_baseline"] = {"value": val, "unit": "cells/s", "cores": 1, "kind": "port",
