@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--cpu-sample-batch", type=int, default=2048)
     ap.add_argument("--no-sdtw", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="e2e leg through the eager module instead of the CUDA graph")
     return ap.parse_args()
 
 
@@ -244,14 +245,20 @@ def run_b200(args):
     # pipeline: step i+1's inputs cross PCIe on a copy stream while step i computes, and every
     # step's H2D copy and D2H loss read happen inside the timed region.
     copy_stream = torch.cuda.Stream(device=dev)
-    bufs = [(torch.empty_like(v_dev), torch.empty_like(t_dev)) for _ in range(2)]
+    graphed = world == 1 and not args.no_graph
+    if graphed:
+        # one CUDA graph per input slot: forward + backward replayed with a single launch
+        gsteps = [milnce_b200.GraphedMILNCEStep(B, K, D, dtype=dtype, device=dev) for _ in range(2)]
+        bufs = [(gs.video, gs.text) for gs in gsteps]
+    else:
+        bufs = [(torch.empty_like(v_dev), torch.empty_like(t_dev)) for _ in range(2)]
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
     e2e_i = [0]
 
     def prefetch(slot):
-        with torch.cuda.stream(copy_stream):
+        with torch.cuda.stream(copy_stream), torch.no_grad():
             copy_stream.wait_event(consumed[slot])  # the step that last read this buffer is done
             bufs[slot][0].copy_(v_host, non_blocking=True)
             bufs[slot][1].copy_(t_host, non_blocking=True)
@@ -267,10 +274,13 @@ def run_b200(args):
         prefetch(slot ^ 1)
         cur = torch.cuda.current_stream()
         cur.wait_event(ready[slot])
-        vi = bufs[slot][0].detach().requires_grad_(True)
-        ti = bufs[slot][1].detach().requires_grad_(True)
-        loss = loss_mod(vi, ti)
-        loss.backward()
+        if graphed:
+            loss, _, _ = gsteps[slot].replay()
+        else:
+            vi = bufs[slot][0].detach().requires_grad_(True)
+            ti = bufs[slot][1].detach().requires_grad_(True)
+            loss = loss_mod(vi, ti)
+            loss.backward()
         consumed[slot].record(cur)
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         cur.synchronize()  # the reference's loss.item() (main_distributed.py:241)
@@ -314,7 +324,8 @@ def run_b200(args):
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3,
-                "pipeline": "double-buffered inputs: the H2D copy of step i+1 overlaps step i on a copy stream"},
+                "pipeline": ("double-buffered inputs: the H2D copy of step i+1 overlaps step i on a copy stream"
+                             + ("; forward+backward replayed as one CUDA graph (GraphedMILNCEStep)" if graphed else ""))},
         "gpu_launches": 8 * (args.steps),
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,

@@ -4,8 +4,8 @@ Drop-ins for the reference's ``loss.MILNCELoss``, ``soft_dtw_cuda.SoftDTW`` and
 ``utils.AllGather``; all arithmetic is in libb200head.so (csrc/, sm_100a only).
 """
 from . import _lib
-from .loss import MILNCELoss
+from .loss import GraphedMILNCEStep, MILNCELoss
 from .soft_dtw_cuda import SoftDTW
 from .utils import AllGather, GatheredMILNCELoss
 
-__all__ = ["MILNCELoss", "SoftDTW", "AllGather", "GatheredMILNCELoss", "_lib"]
+__all__ = ["MILNCELoss", "GraphedMILNCEStep", "SoftDTW", "AllGather", "GatheredMILNCELoss", "_lib"]

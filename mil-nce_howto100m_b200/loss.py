@@ -199,3 +199,52 @@ class MILNCELoss(torch.nn.Module):
 
     def forward(self, video_embd, text_embd):
         return _MILNCEFunction.apply(video_embd, text_embd)
+
+
+class GraphedMILNCEStep:
+    """Loss and input gradients of :class:`MILNCELoss` for a fixed shape, replayed as ONE CUDA graph.
+
+    A training loop that reads the loss on the host every step (the reference does,
+    main_distributed.py:241) is launch-bound around a ~1 ms loss head: the next step's eight kernels
+    are only submitted after the host has seen the previous loss.  Capturing forward + backward
+    once and replaying it removes that submission time from every step.
+
+        step = GraphedMILNCEStep(B, K, D)            # captures on the current device
+        loss, dvideo, dtext = step(video, text)      # copies into the static inputs, replays
+        # or write step.video / step.text directly (e.g. an H2D copy) and call step.replay()
+
+    The returned tensors are the graph's static outputs: they are overwritten by the next call.
+    Gradients are d loss / d input (grad_output = 1), in the input dtype.
+    """
+
+    def __init__(self, B, K, D, dtype=torch.bfloat16, device=None, warmup=3):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.video = torch.zeros(B, D, dtype=dtype, device=dev).requires_grad_(True)
+        self.text = torch.zeros(B * K, D, dtype=dtype, device=dev).requires_grad_(True)
+        mod = MILNCELoss()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):       # warm-up off the capture: builds/loads the library, primes allocators
+            for _ in range(max(1, warmup)):
+                self.video.grad = None
+                self.text.grad = None
+                mod(self.video, self.text).backward()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        self.video.grad = None
+        self.text.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = mod(self.video, self.text)
+            self.loss.backward()
+        self.dvideo = self.video.grad
+        self.dtext = self.text.grad
+
+    def replay(self):
+        self.graph.replay()
+        return self.loss, self.dvideo, self.dtext
+
+    def __call__(self, video_embd, text_embd):
+        with torch.no_grad():
+            self.video.copy_(video_embd, non_blocking=True)
+            self.text.copy_(text_embd, non_blocking=True)
+        return self.replay()

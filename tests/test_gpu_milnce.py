@@ -211,3 +211,21 @@ def test_rows_only_sharding_emulated_on_one_gpu():
     # float32 inputs are rejected with a clear message (they use the row+column block scheme)
     with pytest.raises(RuntimeError, match="bfloat16"):
         CudaBackend.forward_shard(v.float(), t.float(), 0, b)
+
+
+def test_graphed_step_matches_eager_module():
+    """GraphedMILNCEStep: forward + backward captured once, replayed on new inputs."""
+    B, K, D = 512, 4, 256
+    step = milnce_b200.GraphedMILNCEStep(B, K, D, dtype=torch.bfloat16)
+    mod = milnce_b200.MILNCELoss()
+    for seed in (1, 2):
+        g = torch.Generator().manual_seed(seed)
+        v = (torch.randn(B, D, generator=g) * 0.3).bfloat16().cuda()
+        t = (torch.randn(B * K, D, generator=g) * 0.3).bfloat16().cuda()
+        loss, dv, dt = step(v, t)
+        ve, te = v.clone().requires_grad_(True), t.clone().requires_grad_(True)
+        ref = mod(ve, te)
+        ref.backward()
+        torch.cuda.synchronize()
+        assert loss.item() == ref.item()
+        assert torch.equal(dv, ve.grad) and torch.equal(dt, te.grad)
