@@ -94,6 +94,10 @@ def test_golden_fixture(path, dtype):
     (1000, 3, 264, 0.2),    # ragged tiles, odd K
     (129, 1, 8, 1.0),       # K = 1, tiny D
     (5, 7, 24, 0.4),        # fewer rows than a tile
+    (300, 2, 136, 0.3),     # K = 2: column statistics pre-summed in pairs (EpiRowColT<2>)
+    (260, 8, 72, 0.3),      # K = 8: EpiRowColT<8>, ragged second tile
+    (512, 2, 128, 1.5),     # K = 2 with logits in the hundreds: exact per-column / per-row fallbacks
+    (384, 8, 64, 2.0),      # K = 8, same
 ])
 def test_random_shapes(B, K, D, scale, dtype):
     g = torch.Generator().manual_seed(B + K + D)
