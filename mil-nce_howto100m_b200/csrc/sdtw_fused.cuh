@@ -43,14 +43,14 @@ constexpr float COS_EPS_F = 1e-8f;
 constexpr int DS = 64;         // row stride of the DP tiles (see FwdSmem)
 constexpr int WRING = 8;       // backward: weights are fetched this many steps ahead
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
+// x = hi + lo with hi a tf32 value (10 mantissa bits) rounded to nearest, lo = x - hi exact in fp32.
+// Integer add-and-mask instead of cvt.rna.tf32.f32: on sm_100a the cvt expands to a ~5-instruction
+// select sequence, and the two converts per element were three quarters of the instructions of
+// the MMA loops (ncu source page).  The tensor core reads only the top 19 bits of lo (truncation);
+// |lo| <= 2^-11 |x|, so that costs <= 2^-21 |x| per product, the same order as fp32 accumulation.
 __device__ __forceinline__ void split_tf32(float x, uint32_t &hi, uint32_t &lo) {
-    hi = to_tf32(x);
-    lo = to_tf32(x - __uint_as_float(hi));
+    hi = (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
 }
 // D(16x8) += A(16x8, row) . B(8x8, col), tf32 inputs, fp32 accumulate
 __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
