@@ -578,10 +578,13 @@ int num_sms() {
 template <class Epi, bool A_MN = false, int MB = 1, bool N_FAST = false>
 int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                 int chunk_iters, const typename Epi::Params &ep, cudaStream_t stream,
-                const char *what) {
+                const char *what, int a_plane_rows = 0, int a_plane_cols = 0) {
     using L = tc::SmemLayout<BLOCK_N, Epi::STAGE_BYTES, MB>;
     CUtensorMap ma, mb;
-    int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
+    // (MN-major A in planes: the matrix is a_plane_rows x (planes * a_plane_cols), see GemmShape)
+    const uint64_t a_rows = a_plane_rows > 0 ? (uint64_t)a_plane_rows : (uint64_t)Kd;
+    const uint64_t a_cols = a_plane_rows > 0 ? (uint64_t)(Kd / a_plane_rows) * a_plane_cols : (uint64_t)M;
+    int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, a_rows, a_cols, (uint64_t)lda, 64)
                   : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
                                            tc::BLOCK_M);
     if (rc) return rc;
@@ -591,7 +594,7 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int tiles = ((M + MB * tc::BLOCK_M - 1) / (MB * tc::BLOCK_M)) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    tc::GemmShape shape{M, N, Kd, chunk_iters};
+    tc::GemmShape shape{M, N, Kd, chunk_iters, a_plane_rows, a_plane_cols};
     kern<<<grid, tc::num_threads<Epi>(), L::TOTAL, stream>>>(ma, mb, shape, ep);
     B200_LAUNCH_OK(what);
     return 0;
@@ -621,7 +624,7 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
     const int max_pairs = num_sms() / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
-    tc::GemmShape shape{M, N, Kd, 0};
+    tc::GemmShape shape{M, N, Kd, 0, 0, 0};
     (void)what;
     // short reductions with an epilogue-heavy functor: keep A resident, stream only B
     // (not for EpiG: its 32 KB store-staging buffer leaves only three ring stages next to the resident A,
@@ -835,7 +838,15 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                     "milnce dtext GEMM (MN-major G)");
         return rc;
     }
-    // fp32 inputs (hi/lo planes): the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
+    // fp32 inputs (hi/lo planes).  Single-GPU case with B a multiple of 64: read the planes of G
+    // ([hi | lo | hi] along its columns) as an MN-major A operand, plane by plane along the
+    // reduction, against Vt ([hi | hi | lo] along ITS reduction index): no G^T, no second S pass.
+    if (p.n == p.B && p.B % tc::BLOCK_K == 0) {
+        return launch_gemm<tc::EpiStore, true, 1, true>(g, p.ld_g, vt, p.ld_vt, (int)p.BK, p.D, p.P * p.B,
+                                                        p.chunk_g, sd, st, "milnce dtext GEMM (MN-major planes)",
+                                                        p.B, (int)p.BK);
+    }
+    // otherwise the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
     tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, tc::make_fastdiv(p.K), 0, tc::make_fastdiv(1), &sc->inv_ss,
                         fast};
     rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,

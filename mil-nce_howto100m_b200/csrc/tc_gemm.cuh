@@ -192,6 +192,21 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// the same with the descriptors given as low words (see smem_desc_lo)
+__device__ __forceinline__ void umma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 da, db;\n"
+        "mov.b64 da, {%1, %5};\n"
+        "mov.b64 db, {%2, %5};\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(SMEM_DESC_HI)
+        : "memory");
+}
 // Arrives on `bar` once all previously issued MMAs of this thread have completed.
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile(
@@ -879,6 +894,11 @@ struct GemmShape {
     // core's fp32 accumulation truncates, which biases long K loops (measured:
     // 1e-4 relative after 6144 MMA steps); short chunks keep it below 1e-6.
     int chunk_iters;
+    // MN-major A made of K-planes laid side by side (the fp32-accurate gradient tile matrix,
+    // planes [hi | lo | hi] along its columns): k-row kr of the reduction lives at row
+    // kr % a_plane_rows, column offset (kr / a_plane_rows) * a_plane_cols.  0 = one plane.
+    // (a_plane_rows must be a multiple of BLOCK_K.)
+    int a_plane_rows, a_plane_cols;
 };
 
 // threads per CTA: TMA warp + MMA warp + 4 * PARTS epilogue warps
@@ -968,30 +988,39 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (convergent warp, one lane issues) =====================
+        {
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 const int m_blk = N_FAST ? t / num_n : t % num_m;
                 const int n_blk = N_FAST ? t % num_n : t / num_m;
                 for (int kb = 0; kb < k_iters; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
-                    uint8_t *sa = smem + stage * L::STAGE_BYTES;
-                    if (A_MN) {
+                    mbar_wait_warp(&empty_bar[stage], phase ^ 1);
+                    if (elect_one()) {
+                        mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+                        uint8_t *sa = smem + stage * L::STAGE_BYTES;
+                        if (A_MN) {
+                            int krow = kb * BLOCK_K, col_off = 0;
+                            if (shape.a_plane_rows > 0) {
+                                const int pl = krow / shape.a_plane_rows;
+                                krow -= pl * shape.a_plane_rows;
+                                col_off = pl * shape.a_plane_cols;
+                            }
 #pragma unroll
-                        for (int sl = 0; sl < 2 * MB; ++sl)  // 64-wide slabs of the M index
-                            tma_load_2d(sa + sl * (BLOCK_K * 128), &map_a, &full_bar[stage],
-                                        m_blk * TILE_M + sl * 64, kb * BLOCK_K);
-                    } else {
+                            for (int sl = 0; sl < 2 * MB; ++sl)  // 64-wide slabs of the M index
+                                tma_load_2d(sa + sl * (BLOCK_K * 128), &map_a, &full_bar[stage],
+                                            col_off + m_blk * TILE_M + sl * 64, krow);
+                        } else {
 #pragma unroll
-                        for (int rb = 0; rb < MB; ++rb)
-                            tma_load_2d(sa + rb * (BLOCK_M * BLOCK_K * 2), &map_a, &full_bar[stage],
-                                        kb * BLOCK_K, m_blk * TILE_M + rb * BLOCK_M);
+                            for (int rb = 0; rb < MB; ++rb)
+                                tma_load_2d(sa + rb * (BLOCK_M * BLOCK_K * 2), &map_a, &full_bar[stage],
+                                            kb * BLOCK_K, m_blk * TILE_M + rb * BLOCK_M);
+                        }
+                        tma_load_2d(sa + L::A_BYTES, &map_b, &full_bar[stage], kb * BLOCK_K,
+                                    n_blk * BLOCK_N);
                     }
-                    tma_load_2d(sa + L::A_BYTES, &map_b, &full_bar[stage], kb * BLOCK_K,
-                                n_blk * BLOCK_N);
+                    __syncwarp();
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -1000,54 +1029,50 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (convergent warp, one lane issues; see mbar_wait_warp) ====
+        {
             constexpr uint32_t idesc = make_idesc_f16(BLOCK_M, BLOCK_N, A_MN ? 1 : 0);
+            constexpr uint32_t A_STEP = A_MN ? (UMMA_K * 128 / 16) : 2;
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0;  // accumulator-chunk counter: buffer = cc & 1
+            const uint32_t smem_base = smem_u32(smem);
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
                     const uint32_t buf = cc & 1;
-                    mbar_wait(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
+                    mbar_wait_warp(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
                     tcgen05_fence_after();
                     const uint32_t tmem_d = tmem_base + buf * ACC_COLS;
                     const int kb0 = ck * chunk_iters;
                     const int kb1 = min(k_iters, kb0 + chunk_iters);
                     for (int kb = kb0; kb < kb1; ++kb) {
-                        mbar_wait(&full_bar[stage], phase);
+                        mbar_wait_warp(&full_bar[stage], phase);
                         tcgen05_fence_after();
-                        const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-                        const uint64_t bdesc = make_smem_desc(sa + L::A_BYTES);
+                        const uint32_t sa = smem_base + (uint32_t)(stage * L::STAGE_BYTES);
+                        const uint32_t b_lo = smem_desc_lo(sa + L::A_BYTES);
+                        if (elect_one()) {
 #pragma unroll
-                        for (int rb = 0; rb < MB; ++rb) {
-                            const uint32_t sarb = sa + rb * (BLOCK_M * BLOCK_K * 2);
-                            const uint32_t td = tmem_d + rb * BLOCK_N;
-                            if (A_MN) {
-                                // slabs of 64 m are 8 KB apart; a UMMA_K step is 16 rows = 2048 B
-                                const uint64_t adesc = make_smem_desc_mn(sarb, BLOCK_K * 128);
+                            for (int rb = 0; rb < MB; ++rb) {
+                                const uint32_t sarb = sa + rb * (BLOCK_M * BLOCK_K * 2);
+                                const uint32_t td = tmem_d + rb * BLOCK_N;
+                                // MN-major: slabs of 64 m are 8 KB apart, a UMMA_K step is 16 rows = 2048 B;
+                                // K-major: +32 bytes per UMMA_K step inside the swizzled 128-byte row
+                                const uint32_t a_lo = A_MN ? smem_desc_mn_lo(sarb, BLOCK_K * 128) : smem_desc_lo(sarb);
+                                umma_f16_lo(td, a_lo, b_lo, idesc, (uint32_t)(kb > kb0));
 #pragma unroll
-                                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                                    umma_f16(td, adesc + (uint64_t)(k * (UMMA_K * 128 / 16)),
-                                             bdesc + (uint64_t)(k * 2), idesc,
-                                             (uint32_t)((kb > kb0) || (k > 0)));
-                            } else {
-                                const uint64_t adesc = make_smem_desc(sarb);
-#pragma unroll
-                                for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                                    // +32 bytes per UMMA_K step inside the swizzled 128-byte row
-                                    umma_f16(td, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2),
-                                             idesc, (uint32_t)((kb > kb0) || (k > 0)));
-                                }
+                                for (int k = 1; k < BLOCK_K / UMMA_K; ++k)
+                                    umma_f16_lo(td, a_lo + k * A_STEP, b_lo + k * 2, idesc, 1u);
                             }
+                            umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
                         }
-                        umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
+                        __syncwarp();
                         if (++stage == STAGES) {
                             stage = 0;
                             phase ^= 1;
                         }
                     }
-                    umma_commit(&tfull_bar[buf]);  // this chunk's partial sum is complete
+                    if (elect_one()) umma_commit(&tfull_bar[buf]);  // this chunk's partial sum is complete
+                    __syncwarp();
                 }
             }
         }
