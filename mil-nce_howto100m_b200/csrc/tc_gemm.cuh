@@ -2,20 +2,22 @@
 //
 //   C[m, n] = sum_k A[m, k] * Bm[n, k]        A (M, Kd), Bm (N, Kd) fp16, K-major
 //
-// One persistent CTA per SM, 320 threads:
+// One persistent CTA per SM, 64 + 32 * (epilogue warps) threads:
 //   warp 0      TMA producer   (cp.async.bulk.tensor -> 128B-swizzled smem ring)
-//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer
-//   warps 2..9  epilogue: tcgen05.ld the fp32 accumulator (one TMEM lane = one output
-//               row, half the tile's columns per thread) into registers, then run the
-//               epilogue functor
+//   warp 1      TMEM allocator + tcgen05.mma issuer
+//               (both run convergent: every lane polls the mbarrier, elect.sync picks the
+//               lane that issues - see mbar_wait_warp for why)
+//   warps 2..   epilogue, 8 or 16 warps chosen by the functor: tcgen05.ld the fp32
+//               accumulator (one TMEM lane = one output row, a 32- or 64-column part per
+//               thread) into registers, then run the epilogue functor
 // Accumulators are double-buffered in TMEM (2 x BLOCK_N columns) and drained to
 // registers per K-chunk, so the epilogue of tile t overlaps the MMAs of tile t+1
 // and long K loops are summed in fp32 registers (round-to-nearest) rather than
 // inside the tensor core (which truncates).
 //
 // The loss kernels never write C: their epilogues reduce the tile on the fly
-// (row log-sum-exp for the MIL-NCE forward, the softmax-gradient tile G for the
-// backward).  This replaces reference loss.py:11 (th.matmul) + :13-18.
+// (row and column log-sum-exp for the MIL-NCE forward, the softmax-gradient tile G for
+// the backward).  This replaces reference loss.py:11 (th.matmul) + :13-18.
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -113,9 +115,6 @@ __device__ __forceinline__ void tcgen05_fence_before() {
 }
 __device__ __forceinline__ void tcgen05_fence_after() {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void epi_bar_sync(int nthreads) {  // named barrier 1: epilogue threads only
-    asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory");
 }
 
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, uint64_t *bar,
@@ -335,12 +334,9 @@ struct EpiCtx {
     int m0, n0;        // origin of this thread's sub-tile: row block start, FIRST COLUMN OF ITS HALF
     int m_blk, n_blk;  // tile coordinates
     int half;          // 0 .. PARTS-1: which column part of the 128-wide block
-    int nthreads;      // epilogue threads of this CTA (for the named barrier)
     int M, N;          // problem extent
     int tid;           // row within the tile, 0..127
-    int etid;          // index within the epilogue warps
     int lane, q;       // lane, lane quarter
-    int par;           // tile parity, for double-buffered smem scratch
     float *scratch;    // SCRATCH_FLOATS floats of smem shared by the epilogue warps
     uint8_t *stage;    // Epi::STAGE_BYTES bytes of smem (this warp's slice starts at warp_slot)
     int warp_slot;     // 0 .. 4*PARTS-1
@@ -1086,14 +1082,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         c.M = shape.M;
         c.N = shape.N;
         c.tid = c.q * 32 + lane;
-        c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
         c.stage = epi_stage;
-        c.nthreads = NUM_EPI_WARPS * 32;
         c.sub = 0;
         c.nsub = 1;
-        uint32_t cc = 0;
-        int runs = 0;  // epilogue invocations so far (parity of the smem scratch buffers)
+        uint32_t cc = 0;  // epilogue invocations so far (parity of the smem scratch buffers)
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             const int m_blk = N_FAST ? t / num_n : t % num_m;
             c.n_blk = N_FAST ? t % num_n : t / num_m;
@@ -1101,8 +1094,6 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             if (MB == 1) {
                 c.m_blk = m_blk;
                 c.m0 = m_blk * BLOCK_M;
-                c.par = runs & 1;
-                ++runs;
                 float acc[HN];
                 for (int ck = 0; ck < n_chunks; ++ck, ++cc) {
                     const uint32_t buf = cc & 1;
@@ -1142,8 +1133,6 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 for (int rb = 0; rb < MB; ++rb) {
                     c.m_blk = m_blk * MB + rb;
                     c.m0 = c.m_blk * BLOCK_M;
-                    c.par = runs & 1;
-                    ++runs;
                     const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * ACC_COLS +
                                            (uint32_t)(rb * BLOCK_N + c.half * HN);
                     float acc[HN];

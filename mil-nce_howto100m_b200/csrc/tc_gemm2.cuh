@@ -8,6 +8,9 @@
 // the leader CTA issues one M=256, N=256 MMA per K=16 step for both SMs, and each SM
 // keeps its 128 x 256 half of the accumulator in its own TMEM (2 x 256 columns,
 // double-buffered).  Epilogues are the same functors as in tc_gemm.cuh.
+// Two kernels: gemm_tn_2cta_kernel streams A and B (any Kd; the gradient GEMMs and the
+// gradient-tile pass), gemm_tn_2cta_astat_kernel keeps A resident for Kd <= 512 (the
+// statistics pass).
 //
 // Synchronisation (barrier objects live at the same smem offsets in both CTAs):
 //   full[s]    leader's only.  Both CTAs' TMA loads complete_tx on it; each producer
@@ -262,13 +265,10 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         c.M = shape.M;
         c.N = shape.N;
         c.tid = c.q * 32 + lane;
-        c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
         c.stage = epi_stage;
-        c.nthreads = NUM_EPI_WARPS * 32;
         c.nsub = 2;
         uint32_t cc = 0;
-        int runs = 0;
         // tile coordinates advance incrementally (no integer division per tile): (fast, slow) are
         // (n, m) in n-fastest order and (m, n) otherwise
         const int fast_n = N_FAST ? num_n : num_m;
@@ -309,8 +309,6 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 c.n_blk = n_blk * 2 + nb;
                 c.sub = nb;
                 c.n0 = c.n_blk * 128 + c.half * HN;
-                c.par = runs & 1;
-                ++runs;
                 const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * PAIR_N +
                                        (uint32_t)(nb * 128 + c.half * HN);
                 float acc[HN];
@@ -530,13 +528,10 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         c.M = shape.M;
         c.N = shape.N;
         c.tid = c.q * 32 + lane;
-        c.etid = (warp - 2) * 32 + lane;
         c.scratch = epi_scratch;
         c.stage = epi_stage;
-        c.nthreads = NUM_EPI_WARPS * 32;
         c.nsub = 2;
         uint32_t cc = 0;
-        int runs = 0;
         auto tile_m_blk = [&](int t) { return (t / num_n) * 2 + (int)rank; };
         auto tile_n_blk = [&](int t) { return t % num_n; };
         const typename Epi::Consts consts = Epi::load_consts(ep);
@@ -560,8 +555,6 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
                 c.n_blk = n_blk * 2 + nb;
                 c.sub = nb;
                 c.n0 = c.n_blk * 128 + c.half * HN;
-                c.par = runs & 1;
-                ++runs;
                 const uint32_t taddr = tmem_base + ((uint32_t)(c.q * 32) << 16) + buf * PAIR_N +
                                        (uint32_t)(nb * 128 + c.half * HN);
                 float acc[HN];
