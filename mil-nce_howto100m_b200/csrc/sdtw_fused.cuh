@@ -18,6 +18,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 namespace fused {
 
 #ifdef SDTW_PROFILE
@@ -41,7 +43,10 @@ constexpr int BK = 64;         // backward feature chunk
 constexpr int BS = BK + 8;     // smem row stride (floats)
 constexpr float COS_EPS_F = 1e-8f;
 constexpr int DS = 64;         // row stride of the DP tiles (see FwdSmem)
-constexpr int WRING = 8;       // backward: weights are fetched this many steps ahead
+#ifndef SDTW_WRING
+#define SDTW_WRING 8
+#endif
+constexpr int WRING = SDTW_WRING;  // backward: weights are fetched this many steps ahead
 
 // x = hi + lo with hi a tf32 value (10 mantissa bits) rounded to nearest, lo = x - hi exact in fp32.
 // Integer add-and-mask instead of cvt.rna.tf32.f32: on sm_100a the cvt expands to a ~5-instruction
@@ -368,6 +373,7 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
             }
         }
     }
+    SDTW_STAMP(4);
 }
 
 struct BwdSmem {
@@ -426,50 +432,74 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
         // a lane only ever reads slots it filled itself, so cp.async.wait_group is all the
         // synchronisation needed (register double-buffering exposed the load latency on every
         // step: 1800 cycles per step measured).
-        auto fetch_w = [&](int p) {
-            const int j = p - r;
-            const bool okw = (p >= 0) && (r < N) && (j >= 0) && (j < M);
-            const float4 *src = cb + (okw ? (size_t)p * N + r : 0);
-            cp_async16(&s.wring[(p + 2 * WRING * T) % WRING][r], src, okw ? 16 : 0);
+        // A lone warp pays ~5-6 cycles per instruction here, 127 times, so the loop body is pared
+        // down to the recurrence:
+        //  - the saved weights (L2/HBM, ~1 us away) stream through a per-lane shared-memory ring
+        //    filled by cp.async WRING steps ahead; the loop is unrolled WRING times so every ring
+        //    slot is an immediate offset (the rolled loop spent ~12 instructions per step on slot
+        //    arithmetic).  Register prefetch is not an option at this depth: a warp has six
+        //    load scoreboards, so eight loads in flight make each wait cover a younger load
+        //    (measured 600 cycles per step);
+        //  - no validity test on the recurrence: the weights of pruned, unreachable and
+        //    out-of-range cells are zero (the forward stores zeros, cp.async zero-fills), so their
+        //    E comes out as 0.
+        const unsigned mrow = (r < N) ? (unsigned)M : 0u;       // (unsigned)j < mrow  <=>  cell (r, j) exists
+        const float4 *src = cb + (size_t)(steps - 1) * N + r;   // weights of the step being fetched
+        const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&s.wring[0][r]);
+        auto fetch_w = [&](int p, int slot) {                   // slot is a compile-time constant at every call
+            const bool okw = (unsigned)(p - r) < mrow;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ring0 + (uint32_t)(slot * (int)sizeof(float4) * T)),
+                         "l"(okw ? src : cb), "r"(okw ? 16 : 0)
+                         : "memory");
             cp_async_commit();
+            src -= N;
         };
 #pragma unroll
-        for (int k = 0; k < WRING; ++k) fetch_w(steps - 1 - k);
-        for (int p = steps - 1; p >= 0; --p) {
-            cp_async_wait<WRING - 1>();
-            float4 w = s.wring[p % WRING][r];
-            fetch_w(p - WRING);
-            // row r+1, published at step p+1
-            float nu = __shfl_down_sync(0xffffffffu, pu, 1);
-            float nd = __shfl_down_sync(0xffffffffu, pd, 1);
-            if (lane == 31) {
-                nu = 0.f;
-                nd = 0.f;
-                if (warp == 0 && p + 1 <= steps - 1) {
-                    unsigned long long v;
-                    while ((v = mb[p + 1]) == MB_EMPTY) __nanosleep(20);
-                    nu = __int_as_float((int)(unsigned)(v & 0xffffffffull));
-                    nd = __int_as_float((int)(unsigned)(v >> 32));
+        for (int k = 0; k < WRING; ++k) fetch_w(steps - 1 - k, k);
+        // E[N-1, M-1] = 1 enters through `left` (nothing else feeds the corner)
+        const bool corner_ok = !((bandwidth > 0.f) && (fabsf((float)(N - M)) > bandwidth));
+        if (r == N - 1 && corner_ok) left = 1.f;
+        auto wave = [&](auto lead_tag) {
+            constexpr bool LEAD = decltype(lead_tag)::value;    // warp 1 publishes, warp 0 consumes
+            for (int p0 = steps - 1; p0 >= 0; p0 -= WRING) {
+                float *arow = &s.A[r][0] + (p0 - r);            // &A[r][j], j = p - r
+#pragma unroll
+                for (int k = 0; k < WRING; ++k) {
+                    const int p = p0 - k;
+                    if (p < 0) break;
+                    cp_async_wait<WRING - 1>();
+                    const float4 wk = s.wring[k][r];
+                    fetch_w(p - WRING, k);
+                    // row r+1, published at step p+1
+                    float nu = __shfl_down_sync(0xffffffffu, pu, 1);
+                    float nd = __shfl_down_sync(0xffffffffu, pd, 1);
+                    if (lane == 31) {
+                        nu = 0.f;
+                        nd = 0.f;
+                        if (!LEAD && p + 1 <= steps - 1) {
+                            unsigned long long v;
+                            while ((v = mb[p + 1]) == MB_EMPTY) __nanosleep(20);
+                            nu = __int_as_float((int)(unsigned)(v & 0xffffffffull));
+                            nd = __int_as_float((int)(unsigned)(v >> 32));
+                        }
+                    }
+                    const float e = nu + left + nd_prev;
+                    nd_prev = nd;
+                    left = e * wk.z;
+                    pu = e * wk.y;
+                    pd = e * wk.x;
+                    if (LEAD && lane == 0) {
+                        // a NaN pair with all bits set would alias the sentinel: canonicalise the payload
+                        unsigned long long v = ((unsigned long long)(unsigned)__float_as_int(pd) << 32) |
+                                               (unsigned)__float_as_int(pu);
+                        if (v == MB_EMPTY) v = 0x7fc000007fc00000ull;
+                        mb[p] = v;
+                    }
+                    if ((unsigned)(p - r) < mrow) arow[-k] = e;  // raw E; turned into gradient coefficients below
                 }
             }
-            const int j = p - r;
-            const bool act = (r < N) && (j >= 0) && (j < M);
-            const bool ok = act && !((bandwidth > 0.f) && (fabsf((float)(r - j)) > bandwidth));
-            float e = 0.f;
-            if (ok) e = (r == N - 1 && j == M - 1) ? 1.f : (nu + left + nd_prev);
-            nd_prev = nd;
-            left = e * w.z;
-            pu = e * w.y;
-            pd = e * w.x;
-            if (warp == 1 && lane == 0) {
-                // a NaN pair with all bits set would alias the sentinel: canonicalise the payload
-                unsigned long long v = ((unsigned long long)(unsigned)__float_as_int(pd) << 32) |
-                                       (unsigned)__float_as_int(pu);
-                if (v == MB_EMPTY) v = 0x7fc000007fc00000ull;
-                mb[p] = v;
-            }
-            if (act) s.A[r][j] = e;  // raw E; turned into gradient coefficients below
-        }
+        };
+        if (warp == 1) wave(std::true_type{}); else wave(std::false_type{});
         SDTW_STAMP(9);
     }
     __syncthreads();

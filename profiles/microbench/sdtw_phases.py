@@ -2,7 +2,7 @@
 import ctypes, os, sys
 import torch
 here = os.path.dirname(os.path.abspath(__file__))
-lib = ctypes.CDLL(os.path.join(here, "libb200head_prof.so"))
+lib = ctypes.CDLL(os.environ.get("B200HEAD_LIB") or os.path.join(here, "libb200head_prof.so"))
 lib.sdtw_aux_bytes.restype = ctypes.c_size_t
 B, N, M, d = 256, 64, 64, 512
 torch.manual_seed(0)
@@ -21,5 +21,5 @@ torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 16)()
 lib.sdtw_debug_read(buf)
 t = list(buf)
-print("fwd: mma %d  tile %d  dp %d  (cycles, block 0)" % (t[1] - t[0], t[2] - t[1], t[3] - t[2]))
+print("fwd: mma %d  tile %d  dp %d  weights+R %d  (cycles, block 0)" % (t[1] - t[0], t[2] - t[1], t[3] - t[2], t[4] - t[3]))
 print("bwd: dp %d  scale %d  gemm %d" % (t[9] - t[8], t[10] - t[9], t[11] - t[10]))
