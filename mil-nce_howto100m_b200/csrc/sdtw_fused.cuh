@@ -127,6 +127,12 @@ struct FwdSmem {
 // store/prefetch of the producer and tripled the step time): it spins until the entry
 // differs from the sentinel.
 constexpr unsigned long long MB_EMPTY = 0xffffffffffffffffull;
+// ~32 cycles off the shared-memory port between two polls of a mailbox entry
+__device__ __forceinline__ void spin_pause() {
+    const long long t0 = clock64();
+    while (clock64() - t0 < 32) {
+    }
+}
 
 // ---- scaled linear-domain soft-min recurrence ----
 // With P = exp(-R/gamma) the recurrence R = D + softmin_gamma(Ra, Rb, Rc) becomes
@@ -270,7 +276,10 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
             const double xx = -(double)v * inv_g2;
             const double fl = floor(xx);
             s.We[i][j] = (int)fl;
-            s.Wf[i][j] = exp2f((float)(xx - fl));
+            // a Sakoe-Chiba-pruned cell (soft_dtw_cuda.py:60) gets weight 0: the wavefront then needs no
+            // per-step bandwidth test, P = sum * 0 = 0 marks the cell unreachable
+            const bool pruned = (bandwidth > 0.f) && (fabsf((float)(i - j)) > bandwidth);
+            s.Wf[i][j] = pruned ? 0.f : exp2f((float)(xx - fl));
         }
     if (KIND == 0 && tid < 128) {
         if (tid < 64) { if (tid < N) nx_out[(size_t)b * N + tid] = s.nx[tid]; }
@@ -302,48 +311,60 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
         const int r = tid;  // row
         const PVal zero = {0.f, E_ZERO};
         PVal left = zero, up_prev = zero;
+        if (r == 0) { up_prev.f = 1.f; up_prev.e = 0; }      // R[0,0] = 0 of the reference: the diagonal input of cell (0,0)
         volatile unsigned long long *mb = s.mb;
-        // software-pipelined operands of the next step (off the dependency chain)
-        float wfn = 1.f;
+        const unsigned mrow = (r < N) ? (unsigned)M : 0u;    // (unsigned)j < mrow  <=>  cell (r, j) exists
+        // running pointers at column j = p - r of this lane's row (no index arithmetic in the loop)
+        const float *wfp = &s.Wf[r][0] - r;
+        const int *wep = &s.We[r][0] - r;
+        float *pfp = &Pf[r][0] - r;
+        int *pep = &Pe[r][0] - r;
+        // operands of the next step are fetched one step ahead (off the dependency chain); a cell that
+        // does not exist gets weight 0 and so does a pruned one (see the tile phase)
+        float wfn = 0.f;
         int wen = 0;
-        if (r == 0 && N > 0) { wfn = s.Wf[0][0]; wen = s.We[0][0]; }
-        for (int p = 0; p < steps; ++p) {
-            const int j = p - r;
-            const bool act = (r < N) && (j >= 0) && (j < M);
-            const float wf = wfn;
-            const int we = wen;
-            {
-                const int jn = j + 1;
-                if ((r < N) && jn >= 0 && jn < M) { wfn = s.Wf[r][jn]; wen = s.We[r][jn]; }
-            }
-            PVal up;  // row r-1 at step p-1
-            up.f = __shfl_up_sync(0xffffffffu, left.f, 1);
-            up.e = __shfl_up_sync(0xffffffffu, left.e, 1);
-            if (lane == 0) {
-                up = zero;
-                if (warp == 1 && p >= 1) {
-                    unsigned long long v;
-                    // back off between polls: a tight spin on shared memory starves the producer
-                    // warp (measured 3.3x slower steps)
-                    while ((v = mb[p - 1]) == MB_EMPTY) __nanosleep(20);
-                    up.f = __int_as_float((int)(unsigned)(v & 0xffffffffull));
-                    up.e = (int)(unsigned)(v >> 32);
+        if (r == 0 && mrow > 0) { wfn = wfp[0]; wen = wep[0]; }
+        auto wave = [&](auto second_tag) {
+            constexpr bool SECOND = decltype(second_tag)::value;  // warp 1 consumes row 31, warp 0 publishes it
+            for (int p = 0; p < steps; ++p) {
+                const float wf = wfn;
+                const int we = wen;
+                wfn = 0.f;
+                if ((unsigned)(p + 1 - r) < mrow) { wfn = wfp[p + 1]; wen = wep[p + 1]; }
+                PVal up;  // row r-1 at step p-1
+                up.f = __shfl_up_sync(0xffffffffu, left.f, 1);
+                up.e = __shfl_up_sync(0xffffffffu, left.e, 1);
+                if (lane == 0) {
+                    up = zero;
+                    if (SECOND && p >= 1) {
+                        unsigned long long v;
+                        // back off between polls: a tight spin on shared memory starves the producer warp
+                        // (measured 3.3x slower steps), a __nanosleep costs ~500 cycles to wake from
+                        while ((v = mb[p - 1]) == MB_EMPTY) spin_pause();
+                        up.f = __int_as_float((int)(unsigned)(v & 0xffffffffull));
+                        up.e = (int)(unsigned)(v >> 32);
+                    }
                 }
+                // the cell (sdtw_cell without the weights): aligned sum of the three inputs times w
+                const int emax = max(up_prev.e, max(up.e, left.e));
+                const float sum = up_prev.f * pow2_nonpos(up_prev.e - emax) +
+                                  (up.f * pow2_nonpos(up.e - emax) + left.f * pow2_nonpos(left.e - emax));
+                const float pn = sum * wf;  // in [1, 12), or 0: unreachable / pruned / outside
+                const int bits = __float_as_int(pn);
+                PVal nv;
+                nv.e = (pn > 0.f) ? emax + we + ((bits >> 23) - 127) : E_ZERO;
+                nv.f = (pn > 0.f) ? __int_as_float((bits & 0x007fffff) | 0x3f800000) : 0.f;
+                if (!SECOND && lane == 31)
+                    mb[p] = ((unsigned long long)(unsigned)nv.e << 32) | (unsigned)__float_as_int(nv.f);
+                if ((unsigned)(p - r) < mrow) {
+                    pfp[p] = nv.f;
+                    pep[p] = nv.e;
+                }
+                up_prev = up;
+                left = nv;
             }
-            PVal dg = up_prev;  // row r-1 at step p-2
-            if (r == 0 && j == 0) { dg.f = 1.f; dg.e = 0; }  // R[0,0] = 0 of the reference
-            const bool ok = act && !((bandwidth > 0.f) && (fabsf((float)(r - j)) > bandwidth));
-            float wa, wb, wc;
-            const PVal nv = sdtw_cell(dg, up, left, wf, we, ok, wa, wb, wc);
-            if (warp == 0 && lane == 31)
-                mb[p] = ((unsigned long long)(unsigned)nv.e << 32) | (unsigned)__float_as_int(nv.f);
-            if (act) {
-                Pf[r][j] = nv.f;
-                Pe[r][j] = nv.e;
-            }
-            up_prev = up;
-            left = nv;
-        }
+        };
+        if (warp == 1) wave(std::true_type{}); else wave(std::false_type{});
         SDTW_STAMP(3);
     }
     __syncthreads();
@@ -478,7 +499,7 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
                         nd = 0.f;
                         if (!LEAD && p + 1 <= steps - 1) {
                             unsigned long long v;
-                            while ((v = mb[p + 1]) == MB_EMPTY) __nanosleep(20);
+                            while ((v = mb[p + 1]) == MB_EMPTY) spin_pause();
                             nu = __int_as_float((int)(unsigned)(v & 0xffffffffull));
                             nd = __int_as_float((int)(unsigned)(v >> 32));
                         }
