@@ -611,7 +611,7 @@ bool astat_enabled() {
 }
 
 // bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.
-template <class Epi, bool A_MN = false, bool N_FAST = false>
+template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                  const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
     CUtensorMap ma, mb;
@@ -641,11 +641,26 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
         }
     }
     using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
-    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST>;
+    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST, RANGE>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     B200_CUDA_OK(b200::launch_pdl(kern, dim3(2 * pairs), dim3(tc::num_threads<Epi>()), L::TOTAL, stream, ma, mb,
                                   shape, ep));
     return 0;
+}
+
+// Gradient-tile pass: n-fastest contiguous tile ranges per CTA pair (the epilogue keeps its per-row
+// state across the tiles of a row block).  B200HEAD_EPIG_RANGE=0 restores the strided m-fastest order
+// (A/B timing).
+bool epig_range_enabled() {
+    static const bool v = [] {
+        const char *e = getenv("B200HEAD_EPIG_RANGE");
+        return !(e && e[0] == '0');
+    }();
+    return v;
+}
+template <class... Args>
+int launch_epig2(Args... a) {
+    return epig_range_enabled() ? launch_gemm2<tc::EpiG, false, true, true>(a...) : launch_gemm2<tc::EpiG, false, false, false>(a...);
 }
 
 // Stages video/text into the fp16 operands.  When `nom` is non-null the positives' log-sum-exp of
@@ -803,7 +818,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     // row block: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
     const __half *va = vk + (size_t)p.i0 * p.ld_vk;
-    rc = (p.P == 1) ? launch_gemm2<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, gr, st,
+    rc = (p.P == 1) ? launch_epig2(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, gr, st,
                                            "milnce backward row block")
                     : launch_gemm<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, gr, st,
                                             "milnce backward row block");
@@ -828,7 +843,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
             // column block: G2 (B, n*K): row <-> sample r, column c <-> sample (i0*K + c) / K
             tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, tc::make_fastdiv(1), p.i0 * p.K, tc::make_fastdiv(p.K),
                                 &sc->inv_ss, fast};
-            rc = launch_gemm2<tc::EpiG>(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
+            rc = launch_epig2(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
                                         p.n * p.K, Kd, gc, st, "milnce backward column block");
             if (rc) return rc;
             g2 = gt;
@@ -913,7 +928,7 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
-    rc = launch_gemm2<tc::EpiG>(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
+    rc = launch_epig2(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
                                 st, "milnce backward (rows-only shard) G");
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major

@@ -374,11 +374,10 @@ struct EpiStore {
         if (p.alpha_dev) k.alpha *= __ldg(p.alpha_dev);
         return k;
     }
-    __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
-    __device__ static Tile begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k) {
-        Tile t;
+    __device__ static Pre preload(const Params &, const EpiCtx &, int, int, bool) { return Pre{}; }
+    // new_row: the tile's row block differs from the previous tile's (per-row state must be rebuilt)
+    __device__ static void begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k, Tile &t, bool) {
         t.alpha = k.alpha;
-        return t;
     }
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
@@ -508,13 +507,11 @@ struct EpiRowColT {
         k.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
         return k;
     }
-    __device__ static Pre preload(const Params &, const EpiCtx &, int, int) { return Pre{}; }
-    __device__ static Tile begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k) {
-        Tile t;
+    __device__ static Pre preload(const Params &, const EpiCtx &, int, int, bool) { return Pre{}; }
+    __device__ static void begin_tile(const Params &, const EpiCtx &, const Pre &, const Consts &k, Tile &t, bool) {
         t.sc = k.sc;
         t.row_m = -INFINITY;
         t.row_s = 0.f;
-        return t;
     }
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, Tile &t, float (&acc)[HN]) {
@@ -753,10 +750,12 @@ struct EpiG {
         float den_c[4];
     };
     // m0: first row of the 128-row block; n_blk0: first 128-column block of the tile
-    __device__ static Pre preload(const Params &p, const EpiCtx &c, int m0, int n_blk0) {
+    // new_row: that tile starts a new row block (else den_r is not needed again)
+    __device__ static Pre preload(const Params &p, const EpiCtx &c, int m0, int n_blk0, bool new_row) {
         Pre q;
         const int HN = 128 / PARTS;
-        q.den_r = ldg_pinned(p.den + p.rdiv.div(p.row_off + min(m0 + c.tid, c.M - 1)));
+        q.den_r = 0.f;
+        if (new_row) q.den_r = ldg_pinned(p.den + p.rdiv.div(p.row_off + min(m0 + c.tid, c.M - 1)));
 #pragma unroll
         for (int s = 0; s < 2; ++s)
 #pragma unroll
@@ -780,24 +779,25 @@ struct EpiG {
         k.sc = __ldg(p.scale_dev) * LOG2E;
         return k;
     }
-    __device__ static Tile begin_tile(const Params &p, const EpiCtx &c, const Pre &q, const Consts &k) {
-        Tile t;
+    __device__ static void begin_tile(const Params &p, const EpiCtx &c, const Pre &q, const Consts &k, Tile &t,
+                                      bool new_row) {
         t.fast = k.fast;
         t.mid = k.mid;
         t.sc = k.sc;
-        const float dr = q.den_r * LOG2E;
-        t.dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
-        t.ar = t.fast ? fast_exp2(dr - t.mid) : 0.f;
-        const int rs_lo = p.rdiv.div(p.row_off + c.m0);
-        const int rs_hi = p.rdiv.div(p.row_off + min(c.m0 + BLOCK_M, c.M) - 1);
-        t.n_lo = rs_lo * p.cdiv.d - p.col_off;
-        t.n_hi = (rs_hi + 1) * p.cdiv.d - p.col_off;
+        if (new_row) {  // (warp-uniform) everything that depends only on the row block
+            const float dr = q.den_r * LOG2E;
+            t.dr13 = dr - 13.f;  // folds G_SCALE = 2^13 into the exponent
+            t.ar = t.fast ? fast_exp2(dr - t.mid) : 0.f;
+            const int rs_lo = p.rdiv.div(p.row_off + c.m0);
+            const int rs_hi = p.rdiv.div(p.row_off + min(c.m0 + BLOCK_M, c.M) - 1);
+            t.n_lo = rs_lo * p.cdiv.d - p.col_off;
+            t.n_hi = (rs_hi + 1) * p.cdiv.d - p.col_off;
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float dc = q.den_c[i] * LOG2E;  // masked column: +inf -> factor 0 / exponent -inf
             t.cf[i] = t.fast ? fast_exp2(t.mid - dc) : dc;
         }
-        return t;
     }
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
@@ -1122,7 +1122,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // TMEM buffer is free again
                 }
-                typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk), Epi::load_consts(ep));
+                typename Epi::Tile tile_state{};
+                    Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk, true), Epi::load_consts(ep), tile_state, true);
                 Epi::template run<HN>(ep, c, tile_state, acc);
             } else {
                 // two row blocks, one chunk: drain and process them one after the other
@@ -1148,7 +1149,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&tempty_bar[buf]);  // both row blocks drained
                     }
-                    typename Epi::Tile tile_state = Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk), Epi::load_consts(ep));
+                    typename Epi::Tile tile_state{};
+                    Epi::begin_tile(ep, c, Epi::preload(ep, c, c.m0, c.n_blk, true), Epi::load_consts(ep), tile_state, true);
                     Epi::template run<HN>(ep, c, tile_state, acc);
                 }
                 ++cc;

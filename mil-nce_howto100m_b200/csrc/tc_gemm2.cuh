@@ -124,7 +124,10 @@ struct SmemLayout2 {
     static_assert(STAGES >= 3, "pipeline too shallow");
 };
 
-template <class Epi, bool A_MN = false, bool N_FAST = false>
+// N_FAST: n-fastest tile order (else m-fastest).  RANGE (with N_FAST): every pair takes ONE contiguous
+// range of that order instead of every num_pairs-th tile, so it stays on a row block for many tiles
+// (the epilogue keeps its per-row state, A stays hot in L2).
+template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(num_threads<Epi>(), 1)
 gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmShape shape, const typename Epi::Params ep) {
@@ -156,6 +159,10 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const int num_n = (shape.N + PAIR_N - 1) / PAIR_N;
     const int num_tiles = num_m * num_n;
     const int k_iters = (shape.Kd + BLOCK_K - 1) / BLOCK_K;
+    static_assert(!RANGE || N_FAST, "contiguous ranges are defined on the n-fastest order");
+    const int t_begin = RANGE ? (int)((long long)pair * num_tiles / num_pairs) : pair;
+    const int t_end = RANGE ? (int)((long long)(pair + 1) * num_tiles / num_pairs) : num_tiles;
+    const int t_step = RANGE ? 1 : num_pairs;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_a);
@@ -184,7 +191,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = pair; t < num_tiles; t += num_pairs) {
+            for (int t = t_begin; t < t_end; t += t_step) {
                 const int m_blk = N_FAST ? t / num_n : t % num_m;
                 const int n_blk = N_FAST ? t % num_n : t / num_m;
                 const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;        // my rows of A
@@ -223,7 +230,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             uint32_t phase = 0;
             uint32_t cc = 0;
             const uint32_t smem_base = smem_u32(smem);
-            for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
+            for (int t = t_begin; t < t_end; t += t_step, ++cc) {
                 const uint32_t buf = cc & 1;
                 epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
                 mbar_wait_warp(&tempty_bar[buf], ((cc >> 1) & 1) ^ 1);
@@ -272,8 +279,8 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         // tile coordinates advance incrementally (no integer division per tile): (fast, slow) are
         // (n, m) in n-fastest order and (m, n) otherwise
         const int fast_n = N_FAST ? num_n : num_m;
-        int cur_fast = pair % fast_n, cur_slow = pair / fast_n;
-        const int step_fast = num_pairs % fast_n, step_slow = num_pairs / fast_n;
+        int cur_fast = t_begin % fast_n, cur_slow = t_begin / fast_n;
+        const int step_fast = t_step % fast_n, step_slow = t_step / fast_n;
         auto advance = [&](int &f, int &sl) {
             f += step_fast;
             sl += step_slow;
@@ -285,21 +292,25 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         // per-sample values of a tile are loaded one tile ahead (Epi::preload), see EpiG
         const typename Epi::Consts consts = Epi::load_consts(ep);
         typename Epi::Pre pre{};
-        if (pair < num_tiles)
+        typename Epi::Tile tile_state{};
+        c.m0 = -1;  // no row block yet
+        if (t_begin < t_end)
             pre = Epi::preload(ep, c, ((N_FAST ? cur_slow : cur_fast) * 2 + (int)rank) * BLOCK_M,
-                               (N_FAST ? cur_fast : cur_slow) * 2);
-        for (int t = pair; t < num_tiles; t += num_pairs, ++cc) {
+                               (N_FAST ? cur_fast : cur_slow) * 2, true);
+        for (int t = t_begin; t < t_end; t += t_step, ++cc) {
             const int n_blk = N_FAST ? cur_fast : cur_slow;
+            const int prev_m0 = c.m0;
             c.m_blk = (N_FAST ? cur_slow : cur_fast) * 2 + (int)rank;   // 128-row block index of this CTA's rows
             c.m0 = c.m_blk * BLOCK_M;
-            advance(cur_fast, cur_slow);  // now the coordinates of tile t + num_pairs
+            advance(cur_fast, cur_slow);  // now the coordinates of the next tile of this pair
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
             epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
-            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre, consts);
-            if (t + num_pairs < num_tiles)
-                pre = Epi::preload(ep, c, ((N_FAST ? cur_slow : cur_fast) * 2 + (int)rank) * BLOCK_M,
-                                   (N_FAST ? cur_fast : cur_slow) * 2);
+            Epi::begin_tile(ep, c, pre, consts, tile_state, c.m0 != prev_m0);
+            if (t + t_step < t_end) {
+                const int next_m0 = ((N_FAST ? cur_slow : cur_fast) * 2 + (int)rank) * BLOCK_M;
+                pre = Epi::preload(ep, c, next_m0, (N_FAST ? cur_fast : cur_slow) * 2, next_m0 != c.m0);
+            }
             epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
@@ -536,7 +547,7 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         auto tile_n_blk = [&](int t) { return t % num_n; };
         const typename Epi::Consts consts = Epi::load_consts(ep);
         typename Epi::Pre pre{};
-        if (t_begin < t_end) pre = Epi::preload(ep, c, tile_m_blk(t_begin) * BLOCK_M, tile_n_blk(t_begin) * 2);
+        if (t_begin < t_end) pre = Epi::preload(ep, c, tile_m_blk(t_begin) * BLOCK_M, tile_n_blk(t_begin) * 2, true);
         for (int t = t_begin; t < t_end; ++t, ++cc) {
             const int n_blk = tile_n_blk(t);
             c.m_blk = tile_m_blk(t);
@@ -544,8 +555,9 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
             epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
-            typename Epi::Tile tile_state = Epi::begin_tile(ep, c, pre, consts);
-            if (t + 1 < t_end) pre = Epi::preload(ep, c, tile_m_blk(t + 1) * BLOCK_M, tile_n_blk(t + 1) * 2);
+            typename Epi::Tile tile_state{};
+            Epi::begin_tile(ep, c, pre, consts, tile_state, true);
+            if (t + 1 < t_end) pre = Epi::preload(ep, c, tile_m_blk(t + 1) * BLOCK_M, tile_n_blk(t + 1) * 2, true);
             epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
