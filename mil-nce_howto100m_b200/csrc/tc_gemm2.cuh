@@ -548,16 +548,21 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         const typename Epi::Consts consts = Epi::load_consts(ep);
         typename Epi::Pre pre{};
         if (t_begin < t_end) pre = Epi::preload(ep, c, tile_m_blk(t_begin) * BLOCK_M, tile_n_blk(t_begin) * 2, true);
+        typename Epi::Tile tile_state{};
+        c.m0 = -1;
         for (int t = t_begin; t < t_end; ++t, ++cc) {
             const int n_blk = tile_n_blk(t);
+            const int prev_m0 = c.m0;
             c.m_blk = tile_m_blk(t);
             c.m0 = c.m_blk * BLOCK_M;
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
             epi_stamp(Epi::STAMP_KIND, (int)cc, 0);
-            typename Epi::Tile tile_state{};
-            Epi::begin_tile(ep, c, pre, consts, tile_state, true);
-            if (t + 1 < t_end) pre = Epi::preload(ep, c, tile_m_blk(t + 1) * BLOCK_M, tile_n_blk(t + 1) * 2, true);
+            Epi::begin_tile(ep, c, pre, consts, tile_state, c.m0 != prev_m0);
+            if (t + 1 < t_end) {
+                const int next_m0 = tile_m_blk(t + 1) * BLOCK_M;
+                pre = Epi::preload(ep, c, next_m0, tile_n_blk(t + 1) * 2, next_m0 != c.m0);
+            }
             epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
             mbar_wait(&tfull_bar[buf], (cc >> 1) & 1);
             tcgen05_fence_after();
