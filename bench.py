@@ -326,7 +326,7 @@ def run_b200(args):
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3,
                 "pipeline": ("double-buffered inputs: the H2D copy of step i+1 overlaps step i on a copy stream"
                              + ("; forward+backward replayed as one CUDA graph (GraphedMILNCEStep)" if graphed else ""))},
-        "gpu_launches": 8 * (args.steps),
+        "gpu_launches": 7 * (args.steps),
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",

@@ -44,8 +44,7 @@ struct Scalars {
     unsigned int absmax_bits[2];  // |video|max, |text|max as float bits
     float s_video, s_text;        // power-of-two staging scales
     float inv_ss;                 // 1 / (s_video * s_text): un-scales S
-    float alpha_dvideo;           // grad_loss / (B * 2^13 * s_text)
-    float alpha_dtext;            // grad_loss / (B * 2^13 * s_video)
+    float unused_[2];
     float den_mid_log2;           // (min den + max den) / 2 in the log2 domain
     int g_fast;                   // 1: den range small enough for the one-exp gradient tile
     unsigned int ticket;          // blocks of merge_finalize_kernel that are done (last one reduces the loss)
@@ -99,7 +98,7 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.nb_cl = 8 * ((n + 255) / 256);  // 32-row blocks of the owned rows (rows-only sharding)
     p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) / p.cg * 4);
     p.off_diff = take((size_t)n * 4 * 2);  // den - nom, then the merged den
-    p.off_bsum = take((size_t)((n + 31) / 32) * 8);  // per-block partial sums of den - nom (double)
+    p.off_bsum = take((size_t)((n + 31) / 32) * 16);  // per block: sum of den - nom (double), min den, max den
     p.off_g = take((size_t)n * p.ld_g * 2);
     // P == 3: G^T (n*K, P*B) from the transposed pass.  P == 1: G2 = G[all rows, own columns]
     // (B, n*K), read MN-major by the dtext GEMM; not needed at all when n == B.
@@ -161,6 +160,13 @@ __global__ void scalars_forward_kernel(Scalars *s) {
     s->inv_ss = (1.f / sv) * (1.f / st);
 }
 
+// finite and within 60 nats: 2^(den_i - den_j) and its two factors stay in fp32 range
+__device__ __forceinline__ void set_den_range(Scalars *s, float lo, float hi) {
+    const bool ok = (hi - lo) < 60.f && isfinite(hi) && isfinite(lo);
+    s->g_fast = ok ? 1 : 0;
+    s->den_mid_log2 = ok ? 0.5f * (lo + hi) * tc::LOG2E : 0.f;
+}
+
 // one block: gradient scales + the range of den (decides the one-exp path of EpiG)
 __global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, const float *den, int B) {
     __shared__ float smin[32], smax[32];
@@ -186,13 +192,7 @@ __global__ void scalars_backward_kernel(Scalars *s, const float *grad_loss, cons
             lo = fminf(lo, smin[w]);
             hi = fmaxf(hi, smax[w]);
         }
-        const float g = grad_loss[0] / ((float)B * tc::G_SCALE);
-        s->alpha_dvideo = g / s->s_text;
-        s->alpha_dtext = g / s->s_video;
-        // finite and within 60 nats: 2^(den_i - den_j) and its two factors stay in fp32 range
-        const bool ok = (hi - lo) < 60.f && isfinite(hi) && isfinite(lo);
-        s->g_fast = ok ? 1 : 0;
-        s->den_mid_log2 = ok ? 0.5f * (lo + hi) * tc::LOG2E : 0.f;
+        set_den_range(s, lo, hi);
     }
 }
 
@@ -412,9 +412,12 @@ struct MergeFin {
     float *den;         // idem; nullptr: plain merge
     float *diff;        // (n) den - nom
     double *bsum;       // (gridDim.x) per-block sums of diff
+    float *bmin, *bmax; // (gridDim.x) per-block range of den
     unsigned int *ticket;
     float *loss;
     int i0, B;
+    Scalars *range_out; // non-null: the last block also publishes the den range (decides the one-exp
+                        // gradient tile), so that a backward on the same workspace needs no scalar kernel
 };
 __global__ void __launch_bounds__(1024)
 merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict__ part_c, int kc, int n,
@@ -479,9 +482,16 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     }
     if (fin.den == nullptr) return;
     double acc = (double)d;
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    float lo = (w < n) ? fin.den[fin.i0 + w] : INFINITY, hi = (w < n) ? fin.den[fin.i0 + w] : -INFINITY;
+    for (int o = 16; o > 0; o >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
     if (lane == 0) {
         fin.bsum[blockIdx.x] = acc;
+        fin.bmin[blockIdx.x] = lo;
+        fin.bmax[blockIdx.x] = hi;
         __threadfence();
         is_last = (atomicAdd(fin.ticket, 1u) == gridDim.x - 1);
     }
@@ -489,11 +499,22 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     if (!is_last) return;
     __threadfence();
     acc = 0.0;
-    for (int b = lane; b < (int)gridDim.x; b += 32) acc += __ldcg(fin.bsum + b);
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    lo = INFINITY;
+    hi = -INFINITY;
+    for (int b = lane; b < (int)gridDim.x; b += 32) {
+        acc += __ldcg(fin.bsum + b);
+        lo = fminf(lo, __ldcg(fin.bmin + b));
+        hi = fmaxf(hi, __ldcg(fin.bmax + b));
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
     if (lane == 0) {
         fin.loss[0] = (float)(acc / (double)fin.B);
         *fin.ticket = 0;
+        if (fin.range_out != nullptr) set_den_range(fin.range_out, lo, hi);
     }
 }
 
@@ -789,7 +810,11 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         }
         if (rc) return rc;
     }
-    MergeFin fin{nom, den, diff, reinterpret_cast<double *>(ws + p.off_bsum), &sc->ticket, loss, p.i0, p.B};
+    const int nblk = (p.n + 31) / 32;
+    double *bsum = reinterpret_cast<double *>(ws + p.off_bsum);
+    float *bmin = reinterpret_cast<float *>(bsum + nblk);
+    MergeFin fin{nom, den, diff, bsum, bmin, bmin + nblk, &sc->ticket, loss, p.i0, p.B,
+                 p.n == p.B ? sc : nullptr};
     B200_CUDA_OK(b200::launch_pdl(merge_partials_kernel, dim3((p.n + 31) / 32), dim3(1024), 0, st, pr, pc,
                                   p.K / p.cg, p.n, p.nb_r, p.nb_c, (float *)nullptr, fin));
     B200_LAUNCH_OK("milnce finalize");
@@ -806,7 +831,12 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         if (rc) return rc;
     }
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
+    // The den range was published by the forward that left this workspace (single-GPU case); the
+    // gradient scale grad_loss / (B 2^13 s) is formed by the GEMM epilogues from grad_loss itself.
+    // Otherwise (fresh workspace, or den gathered from other ranks) one small kernel derives the range.
+    if (!(reuse && p.n == p.B))
+        B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
+    const float alpha0 = 1.f / ((float)p.B * tc::G_SCALE);
     const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
     const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
@@ -824,7 +854,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                             "milnce backward row block");
     if (rc) return rc;
     // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, alpha0, grad_loss, &sc->s_text, grad_bf16};
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
     rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
@@ -833,7 +863,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
     if (rc) return rc;
-    tc::EpiStore::Params sd{dtext, (long long)p.D, 1.f, &sc->alpha_dtext, grad_bf16};
+    tc::EpiStore::Params sd{dtext, (long long)p.D, alpha0, grad_loss, &sc->s_video, grad_bf16};
     if (p.P == 1) {
         // dtext (n*K, D) = G[:, own columns]^T . V, reading G as an MN-major A operand:
         // nobody materialises G^T.  On one GPU (n == B) the G of the row block is the G needed.
@@ -893,7 +923,7 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
     rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * p.ld_vk,
                        p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
     if (rc) return rc;
-    const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+    const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr};
     merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, 1, p.n, p.nb_r, 0, row_lse + p.i0,
                                                             none);
     merge_partials_kernel<<<(p.B + 31) / 32, 1024, 0, st>>>(nullptr, pc, p.K / p.cg, p.B, 0, p.nb_cl, col_part,
@@ -914,7 +944,7 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     if (parts == 2) {
-        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
+        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
         return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
                                                        "milnce dvideo GEMM (shard)");
     }
@@ -932,11 +962,11 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
                                 st, "milnce backward (rows-only shard) G");
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
-    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f, &sc->alpha_dtext, 0};
+    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_video, 0};
     rc = launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd, st,
                                                 "milnce partial dtext GEMM (shard)");
     if (rc || parts == 1) return rc;
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f, &sc->alpha_dvideo, grad_bf16};
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
     return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
                                                    "milnce dvideo GEMM (shard)");
 }
@@ -1037,7 +1067,7 @@ extern "C" int b200head_gemm_tn_f16(const void *A, const void *Bm, float *C, int
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
     return launch_gemm<tc::EpiStore>(A, lda, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                      "gemm_tn_f16 test hook");
 }
@@ -1050,7 +1080,7 @@ extern "C" int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, in
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
     return launch_gemm<tc::EpiStore, true>(At, ldat, Bm, ldb, M, N, Kd, 16, ep, (cudaStream_t)stream,
                                            "gemm_at_f16 test hook");
 }
@@ -1063,7 +1093,7 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, 0};
+    tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
     return a_transposed ? launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep,
                                                                  (cudaStream_t)stream, "gemm2 test hook")
                         : launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep,

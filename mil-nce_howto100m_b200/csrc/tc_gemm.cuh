@@ -357,7 +357,8 @@ struct EpiStore {
         void *C;  // float32, or bfloat16 when out_bf16 != 0
         long long ldc;
         float alpha;
-        const float *alpha_dev;  // optional device scalar multiplied into alpha
+        const float *alpha_dev;      // optional device scalar multiplied into alpha
+        const float *alpha_div_dev;  // optional device scalar alpha is divided by
         int out_bf16;
     };
     struct Tile {
@@ -372,6 +373,7 @@ struct EpiStore {
         Consts k;
         k.alpha = p.alpha;
         if (p.alpha_dev) k.alpha *= __ldg(p.alpha_dev);
+        if (p.alpha_div_dev) k.alpha /= __ldg(p.alpha_div_dev);
         return k;
     }
     __device__ static Pre preload(const Params &, const EpiCtx &, int, int, bool) { return Pre{}; }
