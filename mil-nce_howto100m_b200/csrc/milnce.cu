@@ -430,34 +430,38 @@ merge_partials_kernel(const float *__restrict__ part_r, const float *__restrict_
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     const int w = blockIdx.x * 32 + lane;
     float m = -INFINITY, s = 0.f;
-    auto push = [&](float v) {
-        if (v > m) {
-            s = s * __expf(m - v) + 1.f;  // m = -inf at the start: exp(-inf) = 0
-            m = v;
-        } else if (v > -INFINITY) {
-            s += __expf(v - m);
+    // eight independent loads at a time; a batch is reduced with its own maximum (eight independent
+    // exponentials) and merged into the running (m, s) once - no 8-long chain of dependent pushes
+    auto push8 = [&](const float (&v)[8]) {
+        float bm = fmaxf(fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3])), fmaxf(fmaxf(v[4], v[5]), fmaxf(v[6], v[7])));
+        if (!(bm > -INFINITY)) return;
+        float bs = 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) bs += __expf(v[u] - bm);  // exp(-inf) = 0 for absent entries
+        if (bm > m) {
+            s = s * __expf(m - bm) + bs;
+            m = bm;
+        } else {
+            s += bs * __expf(bm - m);
         }
     };
     if (w < n) {
-        // batches of four independent loads, then the (serial) merges
-        for (int t = wp; t < nb_r; t += 4 * NW) {
-            float v[4];
+        for (int t = wp; t < nb_r; t += 8 * NW) {
+            float v[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 8; ++u)
                 v[u] = (t + u * NW < nb_r) ? __ldg(part_r + (size_t)(t + u * NW) * n + w) : -INFINITY;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) push(v[u]);
+            push8(v);
         }
         const size_t nk = (size_t)n * kc;
         for (int k = 0; k < kc; ++k) {
             const float *pc = part_c + (size_t)w * kc + k;
-            for (int t = wp; t < nb_c; t += 4 * NW) {
-                float v[4];
+            for (int t = wp; t < nb_c; t += 8 * NW) {
+                float v[8];
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
+                for (int u = 0; u < 8; ++u)
                     v[u] = (t + u * NW < nb_c) ? __ldg(pc + (size_t)(t + u * NW) * nk) : -INFINITY;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) push(v[u]);
+                push8(v);
             }
         }
     }
