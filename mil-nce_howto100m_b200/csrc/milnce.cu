@@ -92,8 +92,10 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     p.off_scal = take(sizeof(Scalars));
     p.off_vk = take((size_t)B * p.ld_vk * 2);
     p.off_tk = take((size_t)p.BK * p.ld_tk * 2);
-    p.off_vt = take((size_t)D * p.ld_vt * 2);
-    p.off_tt = take((size_t)D * p.ld_tt * 2);
+    // transposed operand copies: only the fp32-accurate path (one-CTA kernels) needs them; the CTA-pair
+    // kernel reads text and video as MN-major B operands
+    p.off_vt = take(p.P == 1 ? 0 : (size_t)D * p.ld_vt * 2);
+    p.off_tt = take(p.P == 1 ? 0 : (size_t)D * p.ld_tt * 2);
     p.off_pr = take((size_t)p.nb_r * n * 4);
     p.nb_cl = 8 * ((n + 255) / 256);  // 32-row blocks of the owned rows (rows-only sharding)
     p.off_pc = take(std::max((size_t)p.nb_c * n * K, (size_t)p.nb_cl * (size_t)p.BK) / p.cg * 4);
@@ -285,9 +287,12 @@ stage_bf16_kernel(StageSide sv, StageSide stx, int tiles_v, int D, Scalars *scal
 #pragma unroll
             for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(0.f);
         }
+        if (outt != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) tile[rr][dc + j] = hv[j];
+            for (int j = 0; j < 8; ++j) tile[rr][dc + j] = hv[j];
+        }
     }
+    if (outt == nullptr) return;  // (block-uniform) no transposed copy wanted
     __syncthreads();
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -636,7 +641,7 @@ bool astat_enabled() {
 }
 
 // bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.
-template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false>
+template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false, bool B_MN = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
                  const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
     CUtensorMap ma, mb;
@@ -644,7 +649,9 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
                   : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
                                            tc::BLOCK_M);
     if (rc) return rc;
-    rc = b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, tc::PAIR_N / 2);
+    // B_MN: Bm is passed transposed, (Kd, N) with leading dimension ldb
+    rc = B_MN ? b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)Kd, (uint64_t)N, (uint64_t)ldb, 64)
+              : b200::make_tmap_2d_f16(&mb, Bm, (uint64_t)N, (uint64_t)Kd, (uint64_t)ldb, tc::PAIR_N / 2);
     if (rc) return rc;
     const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
     const int max_pairs = num_sms() / 2;
@@ -654,7 +661,7 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     // short reductions with an epilogue-heavy functor: keep A resident, stream only B
     // (not for EpiG: its 32 KB store-staging buffer leaves only three ring stages next to the resident A and
     // no L1 for its spilled per-tile state: 7680 vs 6310 cycles per tile)
-    constexpr bool CAN_ASTAT = !A_MN && Epi::STAGE_BYTES == 0 && !std::is_same<Epi, tc::EpiStore>::value;
+    constexpr bool CAN_ASTAT = !A_MN && !B_MN && Epi::STAGE_BYTES == 0 && !std::is_same<Epi, tc::EpiStore>::value;
     if constexpr (CAN_ASTAT) {
         if (Kd <= tc::ASTAT_MAX_K_ITERS * tc::BLOCK_K && astat_enabled()) {
             using LA = tc::SmemLayoutAS<Epi::STAGE_BYTES>;
@@ -666,7 +673,7 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
         }
     }
     using L = tc::SmemLayout2<Epi::STAGE_BYTES>;
-    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST, RANGE>;
+    auto kern = tc::gemm_tn_2cta_kernel<Epi, A_MN, N_FAST, RANGE, B_MN>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     B200_CUDA_OK(b200::launch_pdl(kern, dim3(2 * pairs), dim3(tc::num_threads<Epi>()), L::TOTAL, stream, ma, mb,
                                   shape, ep));
@@ -705,8 +712,8 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
             B200_CUDA_OK(b200::launch_pdl(prep_bf16_kernel, dim3(blocks), dim3(wpb * 32), 0, st, video, text, p.B,
                                           p.K, p.D, p.i0, p.n, nom, sc->absmax_bits));
             const int tiles_v = (p.B + 63) / 64, tiles_t = (int)((p.BK + 63) / 64);
-            StageSide sv{video, p.B, vk_, p.ld_vk, vt_, p.ld_vt};
-            StageSide stx{text, (int)p.BK, tk_, p.ld_tk, tt_, p.ld_tt};
+            StageSide sv{video, p.B, vk_, p.ld_vk, nullptr, 0};
+            StageSide stx{text, (int)p.BK, tk_, p.ld_tk, nullptr, 0};
             B200_CUDA_OK(b200::launch_pdl(stage_bf16_kernel, dim3(tiles_v + tiles_t, (p.D + 63) / 64), dim3(256), 0,
                                           st, sv, stx, tiles_v, p.D, sc));
         }
@@ -861,7 +868,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     tc::EpiStore::Params sv{dvideo, (long long)p.D, alpha0, grad_loss, &sc->s_text, grad_bf16};
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
-    rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+    rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
                                             "milnce dvideo GEMM")
                     : launch_gemm<tc::EpiStore, false, 1, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D,
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
@@ -883,7 +890,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
             g2 = gt;
             ld_g2 = p.ld_g2;
         }
-        rc = launch_gemm2<tc::EpiStore, true, true>(g2, ld_g2, vt, p.ld_vt, p.n * p.K, p.D, p.B, sd, st,
+        rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g2, ld_g2, vk, p.ld_vk, p.n * p.K, p.D, p.B, sd, st,
                                     "milnce dtext GEMM (MN-major G)");
         return rc;
     }
@@ -944,12 +951,13 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     // workspace), 3 = both.  Split calls let the caller start the reduce-scatter of dtext
     // while dvideo is still being computed.
     int rc;
-    const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
+    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
+    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     if (parts == 2) {
         tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
-        return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+        return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
                                                        "milnce dvideo GEMM (shard)");
     }
     if (!reuse) {
@@ -957,9 +965,6 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
         if (rc) return rc;
     }
     B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
-    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
-    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
-    const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
     rc = launch_epig2(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
@@ -967,11 +972,11 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
     tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_video, 0};
-    rc = launch_gemm2<tc::EpiStore, true, true>(g, p.ld_g, vt + p.i0, p.ld_vt, (int)p.BK, p.D, p.n, sd, st,
+    rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g, p.ld_g, vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, (int)p.BK, p.D, p.n, sd, st,
                                                 "milnce partial dtext GEMM (shard)");
     if (rc || parts == 1) return rc;
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
-    return launch_gemm2<tc::EpiStore, false, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D, (int)p.BK, sv, st,
+    return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
                                                    "milnce dvideo GEMM (shard)");
 }
 
@@ -1098,10 +1103,14 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
     int rc = b200::check_device();
     if (rc) return rc;
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
-    return a_transposed ? launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep,
-                                                                 (cudaStream_t)stream, "gemm2 test hook")
-                        : launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep,
-                                                                   (cudaStream_t)stream, "gemm2 test hook");
+    // a_transposed: bit 0 = A passed as (Kd, M), bit 1 = Bm passed as (Kd, N)
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (a_transposed & 3) {
+        case 0: return launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
+        case 1: return launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
+        case 2: return launch_gemm2<tc::EpiStore, false, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
+        default: return launch_gemm2<tc::EpiStore, true, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
+    }
 }
 
 extern "C" int milnce_forward_shard(const void *video, const void *text, int B, int K, int D, int dtype,

@@ -174,10 +174,10 @@ __device__ __forceinline__ uint32_t smem_desc_mn_lo(uint32_t saddr, uint32_t lbo
     return ((saddr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
 }
 
-// kind::f16 instruction descriptor: fp16 x fp16 -> fp32; a_mn = 1 selects an
-// MN-major A operand (bit 15), B is always K-major here.
-__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int a_mn = 0) {
-    return (1u << 4) | ((uint32_t)a_mn << 15) | ((uint32_t)(n >> 3) << 17) |
+// kind::f16 instruction descriptor: fp16 x fp16 -> fp32; a_mn / b_mn = 1 select an
+// MN-major A / B operand (bits 15 / 16).
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int a_mn = 0, int b_mn = 0) {
+    return (1u << 4) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) |
            ((uint32_t)(m >> 4) << 24);
 }
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,

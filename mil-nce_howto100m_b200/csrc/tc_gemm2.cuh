@@ -127,7 +127,10 @@ struct SmemLayout2 {
 // N_FAST: n-fastest tile order (else m-fastest).  RANGE (with N_FAST): every pair takes ONE contiguous
 // range of that order instead of every num_pairs-th tile, so it stays on a row block for many tiles
 // (the epilogue keeps its per-row state, A stays hot in L2).
-template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false>
+// B_MN: B is given TRANSPOSED, (Kd, N) row-major (MN-major operand, like A_MN for A): map_b box = 64 n x 64 k
+// rows, this CTA's 128 columns as two 64-wide slabs.  The gradient GEMMs read T and V this way, so no
+// transposed operand copies are staged.
+template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false, bool B_MN = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(num_threads<Epi>(), 1)
 gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const GemmShape shape, const typename Epi::Params ep) {
@@ -211,7 +214,12 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                         } else {
                             tma_load_2d_2sm(sa, &map_a, lead_full, kb * BLOCK_K, m0);
                         }
-                        tma_load_2d_2sm(sa + L::A_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                        if (B_MN) {
+                            tma_load_2d_2sm(sa + L::A_BYTES, &map_b, lead_full, n0, kb * BLOCK_K);
+                            tma_load_2d_2sm(sa + L::A_BYTES + L::B_BYTES / 2, &map_b, lead_full, n0 + 64, kb * BLOCK_K);
+                        } else {
+                            tma_load_2d_2sm(sa + L::A_BYTES, &map_b, lead_full, kb * BLOCK_K, n0);
+                        }
 #endif
                     }
                     __syncwarp();
@@ -225,7 +233,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA; the warp runs convergent, one lane issues) ====
         if (rank == 0) {
-            constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, A_MN ? 1 : 0);
+            constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0;
@@ -241,14 +249,15 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     mbar_wait_warp(&full_bar[stage], phase);
                     tcgen05_fence_after();
                     const uint32_t sa = smem_base + (uint32_t)(stage * L::STAGE_BYTES);
-                    const uint32_t b_lo = smem_desc_lo(sa + L::A_BYTES);
+                    const uint32_t b_lo = B_MN ? smem_desc_mn_lo(sa + L::A_BYTES, L::B_BYTES / 2) : smem_desc_lo(sa + L::A_BYTES);
                     const uint32_t a_lo = A_MN ? smem_desc_mn_lo(sa, L::A_BYTES / 2) : smem_desc_lo(sa);
                     constexpr uint32_t A_STEP = A_MN ? (UMMA_K * 128 / 16) : 2;
+                    constexpr uint32_t B_STEP = B_MN ? (UMMA_K * 128 / 16) : 2;
                     if (elect_one()) {
                         umma_f16_2sm_lo(tmem_d, a_lo, b_lo, idesc, (uint32_t)(kb != 0));
 #pragma unroll
                         for (int k = 1; k < BLOCK_K / UMMA_K; ++k)
-                            umma_f16_2sm_lo(tmem_d, a_lo + k * A_STEP, b_lo + k * 2, idesc, 1u);
+                            umma_f16_2sm_lo(tmem_d, a_lo + k * A_STEP, b_lo + k * B_STEP, idesc, 1u);
                         umma_commit_2sm(&empty_bar[stage]);  // frees this slot in BOTH CTAs
                     }
                     __syncwarp();

@@ -100,7 +100,7 @@ def test_gemm_mn_major_a_matches_torch(M, N, Kd):
     assert err < 2e-6
 
 
-@pytest.mark.parametrize("transposed", [0, 1])
+@pytest.mark.parametrize("transposed", [0, 1, 2, 3])
 @pytest.mark.parametrize("M,N,Kd", [
     (256, 256, 64),      # one pair tile, one k-block
     (256, 256, 512),
@@ -110,18 +110,25 @@ def test_gemm_mn_major_a_matches_torch(M, N, Kd):
     (100, 72, 72),
 ])
 def test_gemm_cta_pair_kernel_matches_torch(M, N, Kd, transposed):
-    """tcgen05.mma.cta_group::2 path: 2-CTA clusters, peer-signalled TMA, multicast commits."""
+    """tcgen05.mma.cta_group::2 path: 2-CTA clusters, peer-signalled TMA, multicast commits.
+    transposed bit 0: A passed as (Kd, M) (MN-major A); bit 1: B passed as (Kd, N) (MN-major B)."""
     lib = milnce_b200._lib.load()
     g = torch.Generator(device="cuda").manual_seed(M * 3 + N * 7 + Kd + transposed)
     ldk = (Kd + 7) // 8 * 8
-    b = torch.randn(N, ldk, generator=g, device="cuda").half()[:, :Kd]
-    if transposed:
+    if transposed & 2:
+        ldn = (N + 7) // 8 * 8
+        b = torch.randn(Kd, ldn, generator=g, device="cuda").half()[:, :N]
+        bt = b.float()                    # (Kd, N)
+    else:
+        b = torch.randn(N, ldk, generator=g, device="cuda").half()[:, :Kd]
+        bt = b.float().t()                # (Kd, N)
+    if transposed & 1:
         ldm = (M + 7) // 8 * 8
         a = torch.randn(Kd, ldm, generator=g, device="cuda").half()[:, :M]
-        ref = a.float().t() @ b.float().t()
+        ref = a.float().t() @ bt
     else:
         a = torch.randn(M, ldk, generator=g, device="cuda").half()[:, :Kd]
-        ref = a.float() @ b.float().t()
+        ref = a.float() @ bt
     c = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
     rc = lib.b200head_gemm2_f16(ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(b.data_ptr()),
                                 ctypes.c_void_p(c.data_ptr()), M, N, Kd, a.stride(0), b.stride(0),
