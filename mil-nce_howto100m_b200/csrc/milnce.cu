@@ -105,7 +105,7 @@ bool make_plan(Plan &p, int B, int K, int D, int dtype, int i0, int n) {
     // P == 3: G^T (n*K, P*B) from the transposed pass.  P == 1: G2 = G[all rows, own columns]
     // (B, n*K), read MN-major by the dtext GEMM; not needed at all when n == B.
     p.ld_g2 = (long long)align_up((size_t)n * K, 8);
-    p.off_gt = take(std::max((size_t)n * K * p.ld_gt * 2, (size_t)B * p.ld_g2 * 2));
+    p.off_gt = take(p.P == 3 ? (size_t)n * K * p.ld_gt * 2 : (n != B ? (size_t)B * p.ld_g2 * 2 : 0));
     p.total = o;
     return true;
 }
