@@ -44,6 +44,13 @@ extern "C" {
 const char *b200head_last_error(void);
 /* ABI version (bumped when a signature changes). */
 int b200head_version(void);
+/* Number of kernels this library has launched in this process so far (all threads, all
+ * devices).  No reference counterpart; bench.py reports the difference over its timed region
+ * as `gpu_launches`.  Kernels replayed from a captured CUDA graph are not seen here: count them
+ * as (launches made during the capture) x (replays).
+ * The library reads no environment variables and has no run-time switches: kernel variants used
+ * for A/B timing exist only as compile-time macros of variant builds (profiles/build_variant.sh). */
+unsigned long long b200head_launch_count(void);
 
 /* ------------------------------------------------------------------------
  * MIL-NCE loss: replaces MILNCELoss.forward (reference loss.py:10-18) and
@@ -92,8 +99,9 @@ int milnce_backward(const void *video, const void *text, const float *den, const
  *             The caller all-gathers row_lse / nom, logsumexp-reduces col_part over ranks and forms
  *             den_j = logaddexp(row_lse_j, col_j), loss = mean(den - nom).
  *   backward: dvideo (n, D) complete for the owned rows, written as dvideo_dtype (F32 or BF16);
- *             dtext_partial (B*K, D) float32 holds only the owned rows' contribution:
- *             reduce-scatter (sum) it over ranks to obtain each rank's (n*K, D) slice.
+ *             dtext_partial (B*K, D), written as dtext_dtype (F32 or BF16), holds only the owned
+ *             rows' contribution: reduce-scatter (sum) it over ranks to obtain each rank's
+ *             (n*K, D) slice (BF16 halves the bytes on the wire; every partial is then rounded once).
  *             parts = 3 computes both.  parts = 1 computes the gradient tile matrix and
  *             dtext_partial only (dvideo may be NULL); a following parts = 2 call with the same
  *             workspace computes dvideo (dtext_partial may be NULL), so the reduce-scatter of
@@ -109,8 +117,9 @@ int milnce_forward_shard(const void *video, const void *text, int B, int K, int 
 int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom, float *loss,
                          void *stream);
 int milnce_backward_shard(const void *video, const void *text, const float *den, const float *nom,
-                          const float *grad_loss, void *dvideo, int dvideo_dtype, float *dtext_partial,
-                          int parts, int B, int K, int D, int dtype, int i0, int n, int reuse_forward_ws,
+                          const float *grad_loss, void *dvideo, int dvideo_dtype, void *dtext_partial,
+                          int dtext_dtype, int parts, int B, int K, int D, int dtype, int i0, int n,
+                          int reuse_forward_ws,
                           void *workspace, size_t workspace_bytes, void *stream);
 
 /* ------------------------------------------------------------------------
@@ -178,7 +187,8 @@ int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, int M, int N,
                          int ldat, int ldb, int ldc, float alpha, void *stream);
 /* Same products through the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 x 256 tiles) that
  * the bf16 path uses; a_transposed bit 0: A is passed as (Kd, M) like b200head_gemm_at_f16, bit 1: Bm is
- * passed as (Kd, N) (MN-major B operand, how the gradient GEMMs read text and video). */
+ * passed as (Kd, N) (MN-major B operand, how the gradient GEMMs read text and video); bit 2: A holds
+ * bfloat16 instead of float16; bit 3: Bm holds bfloat16 (the two operand formats are independent). */
 int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
                        int lda, int ldb, int ldc, float alpha, int a_transposed, void *stream);
 

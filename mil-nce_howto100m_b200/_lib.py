@@ -7,6 +7,8 @@ built or loaded, or a call fails, a ``RuntimeError`` is raised.
 from __future__ import annotations
 
 import ctypes
+import fcntl
+import glob
 import os
 import shutil
 import subprocess
@@ -15,14 +17,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libb200head.so")
 SOURCES = ("capi.cu", "milnce.cu", "sdtw.cu")
-HEADERS = ("common.cuh", "tc_gemm.cuh", os.path.join("..", "..", "include", "b200head.h"))
+PUBLIC_HEADER = os.path.join(os.path.dirname(_HERE), "include", "b200head.h")
 
 F32, BF16 = 0, 1
 DIST_KINDS = {"cosine": 0, "negative_dot": 1, "euclidean": 2}
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-shared", "-Xcompiler", "-fPIC",
+    "-shared", "-Xcompiler", "-fPIC", "-t", "0",
 ]
 
 _lib = None
@@ -32,27 +34,46 @@ def _sources():
     return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
 
+def _deps():
+    """Every file the library is compiled from: csrc/*.cu, csrc/*.cuh and the public header."""
+    return sorted(glob.glob(os.path.join(CSRC, "*.cu")) + glob.glob(os.path.join(CSRC, "*.cuh"))) + [PUBLIC_HEADER]
+
+
 def _stale() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
-    deps = _sources() + [os.path.join(CSRC, h) for h in HEADERS]
-    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in _deps())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/*.cu into libb200head.so for sm_100a (cross-compiles without a GPU)."""
+    """Compile csrc/*.cu into libb200head.so for sm_100a (cross-compiles without a GPU).
+
+    Safe when several processes start at once (torchrun): the compile runs under an exclusive
+    file lock into a temporary file that is renamed over the library, so nobody can load a
+    half-written .so, and the ranks that waited for the lock find a fresh library and skip."""
     if not force and not _stale():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    if not os.path.exists(nvcc):
-        raise RuntimeError("nvcc not found: cannot build libb200head.so")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + _sources()
-    proc = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
-    if proc.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + proc.stdout + proc.stderr)
-    if verbose:
-        print(proc.stderr)
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():   # another process built it while we waited
+                return LIB_PATH
+            if not os.path.exists(nvcc):
+                raise RuntimeError("nvcc not found: cannot build libb200head.so")
+            tmp = f"{LIB_PATH}.tmp.{os.getpid()}"
+            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + _sources()
+            proc = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
+            if proc.returncode != 0:
+                if os.path.exists(tmp):
+                    os.unlink(tmp)
+                raise RuntimeError("nvcc failed:\n" + proc.stdout + proc.stderr)
+            os.replace(tmp, LIB_PATH)
+            if verbose:
+                print(proc.stderr)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
 
 
@@ -63,6 +84,8 @@ def _declare(lib):
     lib.b200head_last_error.argtypes = []
     lib.b200head_version.restype = i32
     lib.b200head_version.argtypes = []
+    lib.b200head_launch_count.restype = c.c_ulonglong
+    lib.b200head_launch_count.argtypes = []
     lib.milnce_workspace_bytes.restype = sz
     lib.milnce_workspace_bytes.argtypes = [i32, i32, i32, i32, i32]
     lib.milnce_forward.restype = i32
@@ -75,8 +98,8 @@ def _declare(lib):
     lib.milnce_shard_combine.restype = i32
     lib.milnce_shard_combine.argtypes = [fp, i32, i32, fp, fp, fp, vp]
     lib.milnce_backward_shard.restype = i32
-    lib.milnce_backward_shard.argtypes = [vp, vp, fp, fp, fp, vp, i32, fp, i32, i32, i32, i32, i32, i32, i32, i32,
-                                          vp, sz, vp]
+    lib.milnce_backward_shard.argtypes = [vp, vp, fp, fp, fp, vp, i32, vp, i32, i32, i32, i32, i32, i32, i32, i32,
+                                          i32, vp, sz, vp]
     lib.sdtw_aux_bytes.restype = sz
     lib.sdtw_aux_bytes.argtypes = [i32, i32, i32, i32]
     lib.sdtw_forward.restype = i32

@@ -1,4 +1,5 @@
 // Error reporting, device check and TMA descriptor construction for libb200head.
+#include <atomic>
 #include <mutex>
 #include <string.h>
 
@@ -96,14 +97,20 @@ int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t
 }  // namespace b200
 
 extern "C" const char *b200head_last_error(void) { return b200::get_error(); }
-extern "C" int b200head_version(void) { return 2; }
+extern "C" int b200head_version(void) { return 3; }
 
 namespace b200 {
-bool pdl_enabled() {
-    static const bool v = [] {
-        const char *e = getenv("B200HEAD_PDL");
-        return e && e[0] == '1';  // opt-in: measured neutral on the benchmark shape (0.993 vs 0.997 ms)
-    }();
-    return v;
-}
+// Programmatic dependent launch measured neutral on the benchmark shape (0.993 vs 0.997 ms), so it
+// is compiled out by default; -DB200_PDL=1 in a variant build turns it on.  No run-time switch.
+#ifndef B200_PDL
+#define B200_PDL 0
+#endif
+bool pdl_enabled() { return B200_PDL != 0; }
+
+static std::atomic<unsigned long long> g_launches{0};
+void note_launches(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 }  // namespace b200
+
+extern "C" unsigned long long b200head_launch_count(void) {
+    return b200::g_launches.load(std::memory_order_relaxed);
+}

@@ -30,9 +30,11 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // kernel of the stream is still draining, so its prologue (barrier set-up, TMEM allocation,
 // descriptor prefetch) and the launch latency overlap that kernel's tail.  Every kernel launched
 // this way executes griddepcontrol.wait (tc::pdl_wait) before it touches global memory, which
-// blocks until the previous grid has completed and its writes are visible.  Off unless B200HEAD_PDL=1
-// is set in the environment: it measured neutral on the benchmark shape, plain launches are the default.
+// blocks until the previous grid has completed and its writes are visible.  Compiled out unless the
+// library is built with -DB200_PDL=1: it measured neutral on the benchmark shape.
 bool pdl_enabled();
+// Every kernel launch the library makes is counted (b200head_launch_count in the C ABI).
+void note_launches(unsigned n);
 template <class... KArgs, class... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                               Args &&...args) {
@@ -46,6 +48,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    note_launches(1);
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 

@@ -322,6 +322,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // bf16 fast path, first pass over the inputs (one launch instead of three): one warp per sample i
+// (absmax_bits == nullptr: the operands go to the tensor cores as they are, only the positives are wanted;
+// the grid then covers the n owned samples, B and i0 are passed as i0 + n and i0)
 // reads video[i] and its K candidates text[iK .. iK+K) once and produces
 //   - the running |x|max of both tensors (atomicMax on the float bits, like absmax_kernel)
 //   - nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs on the original values
@@ -352,8 +354,9 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
             f[2 * j + 1] = v.y;
         }
     };
-    for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < B; i += gridDim.x * wpb) {
+    for (int i = (absmax_bits == nullptr ? i0 : 0) + blockIdx.x * wpb + (threadIdx.x >> 5); i < B; i += gridDim.x * wpb) {
         const bool want_nom = (nom != nullptr) && i >= i0 && i < i0 + n;
+        if (absmax_bits == nullptr && !want_nom) continue;  // positives only: nothing to do for this sample
         const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
         float pm = -INFINITY, ps = 0.f;
 #pragma unroll 2
@@ -382,6 +385,7 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
         }
         if (want_nom && lane == 0) nom[i] = pm + logf(ps);
     }
+    if (absmax_bits == nullptr) return;  // (kernel-uniform)
     mv = warp_max(mv);
     mt = warp_max(mt);
     __shared__ float sv[8], stx[8];
@@ -624,26 +628,25 @@ int launch_gemm(const void *A, long long lda, const void *Bm, long long ldb, int
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     const int tiles = ((M + MB * tc::BLOCK_M - 1) / (MB * tc::BLOCK_M)) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    tc::GemmShape shape{M, N, Kd, chunk_iters, a_plane_rows, a_plane_cols};
+    tc::GemmShape shape{M, N, Kd, chunk_iters, a_plane_rows, a_plane_cols, 0u};
     kern<<<grid, tc::num_threads<Epi>(), L::TOTAL, stream>>>(ma, mb, shape, ep);
+    b200::note_launches(1);
     B200_LAUNCH_OK(what);
     return 0;
 }
 
-// B200HEAD_ASTAT=0 in the environment selects the streaming kernel for the similarity GEMMs too
-// (A/B timing).
-bool astat_enabled() {
-    static const bool v = [] {
-        const char *e = getenv("B200HEAD_ASTAT");
-        return !(e && e[0] == '0');
-    }();
-    return v;
-}
+// Variant builds (profiles/build_variant.sh) can switch the A-stationary statistics kernel off with
+// -DB200_ASTAT=0 for A/B timing; the shipped library has no run-time switches.
+#ifndef B200_ASTAT
+#define B200_ASTAT 1
+#endif
+constexpr bool astat_enabled() { return B200_ASTAT != 0; }
 
 // bf16 mode: CTA-pair kernel (tc_gemm2.cuh), 256 x 256 tiles.
+// fmt: tc::IDESC_A_BF16 / tc::IDESC_B_BF16 when that operand holds bfloat16 instead of float16.
 template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false, bool B_MN = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
-                 const typename Epi::Params &ep, cudaStream_t stream, const char *what) {
+                 const typename Epi::Params &ep, cudaStream_t stream, const char *what, uint32_t fmt = 0) {
     CUtensorMap ma, mb;
     int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
                   : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
@@ -656,7 +659,7 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
     const int max_pairs = num_sms() / 2;
     const int pairs = tiles < max_pairs ? tiles : max_pairs;
-    tc::GemmShape shape{M, N, Kd, 0, 0, 0};
+    tc::GemmShape shape{M, N, Kd, 0, 0, 0, fmt};
     (void)what;
     // short reductions with an epilogue-heavy functor: keep A resident, stream only B
     // (not for EpiG: its 32 KB store-staging buffer leaves only three ring stages next to the resident A and
@@ -681,18 +684,43 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
 }
 
 // Gradient-tile pass: n-fastest contiguous tile ranges per CTA pair (the epilogue keeps its per-row
-// state across the tiles of a row block).  B200HEAD_EPIG_RANGE=0 restores the strided m-fastest order
-// (A/B timing).
-bool epig_range_enabled() {
-    static const bool v = [] {
-        const char *e = getenv("B200HEAD_EPIG_RANGE");
-        return !(e && e[0] == '0');
-    }();
-    return v;
-}
+// state across the tiles of a row block).  -DB200_EPIG_RANGE=0 in a variant build restores the strided
+// m-fastest order (A/B timing).
+#ifndef B200_EPIG_RANGE
+#define B200_EPIG_RANGE 1
+#endif
 template <class... Args>
 int launch_epig2(Args... a) {
-    return epig_range_enabled() ? launch_gemm2<tc::EpiG, false, true, true>(a...) : launch_gemm2<tc::EpiG, false, false, false>(a...);
+    if constexpr (B200_EPIG_RANGE != 0) return launch_gemm2<tc::EpiG, false, true, true>(a...);
+    else return launch_gemm2<tc::EpiG, false, false, false>(a...);
+}
+
+// bfloat16 inputs with 16-byte aligned rows go to the tensor cores AS THEY ARE: tcgen05.mma.kind::f16 takes
+// the format of A and of B separately, so S = V . T^T runs bf16 x bf16 and the gradient GEMMs multiply
+// the fp16 gradient tiles by the bf16 embeddings.  No staged fp16 copy, no |x|max pass, no scale.
+// (-DB200_DIRECT_BF16=0 in a variant build forces the staged path for A/B timing.)
+#ifndef B200_DIRECT_BF16
+#define B200_DIRECT_BF16 1
+#endif
+bool direct_bf16(const Plan &p, const void *video, const void *text) {
+    return B200_DIRECT_BF16 != 0 && p.dtype == B200HEAD_BF16 && p.D % 8 == 0 &&
+           ((((uintptr_t)video) | ((uintptr_t)text)) & 15) == 0;
+}
+// What the GEMMs read: the staged fp16 operands in the workspace, or the caller's bf16 tensors.
+struct Operands {
+    const __half *vk, *tk;      // K-major video (B, ld_vk) and text (BK, ld_tk) (bf16 bits when direct)
+    long long ld_vk, ld_tk;
+    const float *inv_ss, *s_video, *s_text;  // device scalars; null when direct (scale 1)
+    uint32_t fmt_s;             // S = V . T^T:  both operands
+    uint32_t fmt_b;             // gradient GEMMs: the B operand (text or video); A is the fp16 G
+};
+Operands operands(const Plan &p, const void *video, const void *text, uint8_t *ws) {
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    if (direct_bf16(p, video, text))
+        return Operands{(const __half *)video, (const __half *)text, (long long)p.D, (long long)p.D, nullptr, nullptr,
+                        nullptr, tc::IDESC_A_BF16 | tc::IDESC_B_BF16, tc::IDESC_B_BF16};
+    return Operands{reinterpret_cast<const __half *>(ws + p.off_vk), reinterpret_cast<const __half *>(ws + p.off_tk),
+                    p.ld_vk, p.ld_tk, &sc->inv_ss, &sc->s_video, &sc->s_text, 0u, 0u};
 }
 
 // Stages video/text into the fp16 operands.  When `nom` is non-null the positives' log-sum-exp of
@@ -706,6 +734,16 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
     bool fast = false;
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
         fast = (p.D % 8 == 0) && (((uintptr_t)video & 15) == 0) && (((uintptr_t)text & 15) == 0);
+        if (direct_bf16(p, video, text)) {
+            // nothing to stage; only the positives of the owned samples (one warp each)
+            if (nom != nullptr) {
+                const int wpb = 8;
+                B200_CUDA_OK(b200::launch_pdl(prep_bf16_kernel, dim3((p.n + wpb - 1) / wpb), dim3(wpb * 32), 0, st,
+                                              video, text, p.i0 + p.n, p.K, p.D, p.i0, p.n, nom,
+                                              (unsigned int *)nullptr));
+            }
+            return 0;
+        }
         if (fast) {
             const int wpb = 8;
             const int blocks = std::min((p.B + wpb - 1) / wpb, 8 * num_sms());
@@ -725,12 +763,15 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
         absmax_kernel<T><<<(unsigned)std::min<size_t>((ct + 1023) / 1024, 1184), 256, 0, st>>>(
             text, ct, &sc->absmax_bits[1]);
         scalars_forward_kernel<<<1, 1, 0, st>>>(sc);
+        b200::note_launches(5 + (nom != nullptr ? 1 : 0));  // 2 absmax, scalars, 2 staging, positives
         dim3 blk(32, 8);
         dim3 gv((p.D + 31) / 32, (p.B + 31) / 32), gt((p.D + 31) / 32, (unsigned)((p.BK + 31) / 32));
+        // the transposed copies exist only in the three-plane layout (make_plan gives them no room when P == 1)
+        __half *vt_out = (p.P == 1) ? nullptr : vt_, *tt_out = (p.P == 1) ? nullptr : tt_;
         stage_operand_kernel<T><<<gv, blk, 0, st>>>(video, p.B, p.D, &sc->s_video, p.P, true, vk_, p.ld_vk,
-                                                    vt_, p.ld_vt);
+                                                    vt_out, p.ld_vt);
         stage_operand_kernel<T><<<gt, blk, 0, st>>>(text, (int)p.BK, p.D, &sc->s_text, p.P, false, tk_,
-                                                    p.ld_tk, tt_, p.ld_tt);
+                                                    p.ld_tk, tt_out, p.ld_tt);
         if (nom != nullptr) {
             const int warps_per_block = 8;
             finalize_kernel<T><<<(p.n + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, st>>>(
@@ -761,9 +802,9 @@ int check_common(const Plan &p, const void *ws, size_t ws_bytes) {
 template <int G>
 int launch_stats2_g(const float *scale, float *pr, long long ldr, float *pc, long long ldc, const void *A,
                     long long lda, const void *Bm, long long ldb, int M, int N, int Kd, cudaStream_t st,
-                    const char *what) {
+                    const char *what, uint32_t fmt) {
     typename tc::EpiRowColT<G>::Params e{pr, ldr, pc, ldc, scale};
-    return launch_gemm2<tc::EpiRowColT<G>>(A, lda, Bm, ldb, M, N, Kd, e, st, what);
+    return launch_gemm2<tc::EpiRowColT<G>>(A, lda, Bm, ldb, M, N, Kd, e, st, what, fmt);
 }
 template <class... Args>
 int launch_stats2(int cg, Args... a) {
@@ -781,8 +822,8 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
     int rc = stage_inputs<T>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
-    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const Operands o = operands(p, video, text, ws);
+    const __half *vk = o.vk, *tk = o.tk;
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
     float *diff = reinterpret_cast<float *>(ws + p.off_diff);
@@ -792,31 +833,31 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         // one pass over S: row statistic per thread, column statistic by a cross-lane reduction
         const char *what = "milnce forward (fused row+column statistics)";
         if (p.P == 1) {
-            rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, pc, ldc, vk, p.ld_vk, tk, p.ld_tk, p.B,
-                               (int)p.BK, Kd, st, what);
+            rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, ldc, vk, o.ld_vk, tk, o.ld_tk, p.B,
+                               (int)p.BK, Kd, st, what, o.fmt_s);
         } else {
-            tc::EpiRowCol::Params e{pr, (long long)p.n, pc, ldc, &sc->inv_ss};
-            rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tk, p.ld_tk, p.B, (int)p.BK, Kd, p.chunk_s, e, st, what);
+            tc::EpiRowCol::Params e{pr, (long long)p.n, pc, ldc, o.inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(vk, o.ld_vk, tk, o.ld_tk, p.B, (int)p.BK, Kd, p.chunk_s, e, st, what);
         }
         if (rc) return rc;
     } else {
         // sharded: rows [i0, i0+n) x all columns -> row statistic of the owned samples
-        const __half *va = vk + (size_t)p.i0 * p.ld_vk;
+        const __half *va = vk + (size_t)p.i0 * o.ld_vk;
         // all rows x columns of the owned samples -> their column statistic
-        const __half *tb = tk + (size_t)p.i0 * p.K * p.ld_tk;
+        const __half *tb = tk + (size_t)p.i0 * p.K * o.ld_tk;
         if (p.P == 1) {
-            rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, nullptr, 0, va, p.ld_vk, tk, p.ld_tk, p.n,
-                               (int)p.BK, Kd, st, "milnce forward row block");
+            rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, nullptr, 0, va, o.ld_vk, tk, o.ld_tk, p.n,
+                               (int)p.BK, Kd, st, "milnce forward row block", o.fmt_s);
             if (rc) return rc;
-            rc = launch_stats2(p.cg, &sc->inv_ss, nullptr, 0, pc, ldc, vk, p.ld_vk, tb, p.ld_tk, p.B,
-                               p.n * p.K, Kd, st, "milnce forward column block");
+            rc = launch_stats2(p.cg, o.inv_ss, nullptr, 0, pc, ldc, vk, o.ld_vk, tb, o.ld_tk, p.B,
+                               p.n * p.K, Kd, st, "milnce forward column block", o.fmt_s);
         } else {
-            tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, &sc->inv_ss};
-            rc = launch_gemm<tc::EpiRowCol>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, er, st,
+            tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, o.inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, er, st,
                                             "milnce forward row block");
             if (rc) return rc;
-            tc::EpiRowCol::Params ec{nullptr, 0, pc, ldc, &sc->inv_ss};
-            rc = launch_gemm<tc::EpiRowCol>(vk, p.ld_vk, tb, p.ld_tk, p.B, p.n * p.K, Kd, p.chunk_s, ec, st,
+            tc::EpiRowCol::Params ec{nullptr, 0, pc, ldc, o.inv_ss};
+            rc = launch_gemm<tc::EpiRowCol>(vk, o.ld_vk, tb, o.ld_tk, p.B, p.n * p.K, Kd, p.chunk_s, ec, st,
                                             "milnce forward column block");
         }
         if (rc) return rc;
@@ -848,8 +889,8 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     if (!(reuse && p.n == p.B))
         B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const float alpha0 = 1.f / ((float)p.B * tc::G_SCALE);
-    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
-    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const Operands o = operands(p, video, text, ws);
+    const __half *vk = o.vk, *tk = o.tk;
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
     const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
@@ -857,24 +898,24 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     const int Kd = p.P * p.D;
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     // row block: G (n, BK): row r <-> sample i0+r, column c <-> sample c / K
-    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
-    const __half *va = vk + (size_t)p.i0 * p.ld_vk;
-    rc = (p.P == 1) ? launch_epig2(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, gr, st,
-                                           "milnce backward row block")
-                    : launch_gemm<tc::EpiG>(va, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, gr, st,
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), o.inv_ss, fast};
+    const __half *va = vk + (size_t)p.i0 * o.ld_vk;
+    rc = (p.P == 1) ? launch_epig2(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, gr, st,
+                                           "milnce backward row block", o.fmt_s)
+                    : launch_gemm<tc::EpiG>(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, gr, st,
                                             "milnce backward row block");
     if (rc) return rc;
     // dvideo (n, D) = G . T      : A = G (n, P*BK), Bm = Tt (D, P*BK)
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, alpha0, grad_loss, &sc->s_text, grad_bf16};
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, alpha0, grad_loss, o.s_text, grad_bf16};
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
-    rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                            "milnce dvideo GEMM")
+    rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
+                                            "milnce dvideo GEMM", o.fmt_b)
                     : launch_gemm<tc::EpiStore, false, 1, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D,
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
     if (rc) return rc;
-    tc::EpiStore::Params sd{dtext, (long long)p.D, alpha0, grad_loss, &sc->s_video, grad_bf16};
+    tc::EpiStore::Params sd{dtext, (long long)p.D, alpha0, grad_loss, o.s_video, grad_bf16};
     if (p.P == 1) {
         // dtext (n*K, D) = G[:, own columns]^T . V, reading G as an MN-major A operand:
         // nobody materialises G^T.  On one GPU (n == B) the G of the row block is the G needed.
@@ -883,15 +924,15 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
         if (p.n != p.B) {
             // column block: G2 (B, n*K): row <-> sample r, column c <-> sample (i0*K + c) / K
             tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, tc::make_fastdiv(1), p.i0 * p.K, tc::make_fastdiv(p.K),
-                                &sc->inv_ss, fast};
-            rc = launch_epig2(vk, p.ld_vk, tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, p.B,
-                                        p.n * p.K, Kd, gc, st, "milnce backward column block");
+                                o.inv_ss, fast};
+            rc = launch_epig2(vk, o.ld_vk, tk + (size_t)p.i0 * p.K * o.ld_tk, o.ld_tk, p.B,
+                                        p.n * p.K, Kd, gc, st, "milnce backward column block", o.fmt_s);
             if (rc) return rc;
             g2 = gt;
             ld_g2 = p.ld_g2;
         }
-        rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g2, ld_g2, vk, p.ld_vk, p.n * p.K, p.D, p.B, sd, st,
-                                    "milnce dtext GEMM (MN-major G)");
+        rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g2, ld_g2, vk, o.ld_vk, p.n * p.K, p.D, p.B, sd, st,
+                                    "milnce dtext GEMM (MN-major G)", o.fmt_b);
         return rc;
     }
     // fp32 inputs (hi/lo planes).  Single-GPU case with B a multiple of 64: read the planes of G
@@ -903,9 +944,9 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
                                                         p.B, (int)p.BK);
     }
     // otherwise the transposed problem S^T = T . V^T yields G^T (n*K, P*B) row-major
-    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, tc::make_fastdiv(p.K), 0, tc::make_fastdiv(1), &sc->inv_ss,
+    tc::EpiG::Params gc{den, nom, gt, p.ld_gt, (long long)p.B, p.P, p.i0 * p.K, tc::make_fastdiv(p.K), 0, tc::make_fastdiv(1), o.inv_ss,
                         fast};
-    rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * p.ld_tk, p.ld_tk, vk, p.ld_vk, p.n * p.K,
+    rc = launch_gemm<tc::EpiG>(tk + (size_t)p.i0 * p.K * o.ld_tk, o.ld_tk, vk, o.ld_vk, p.n * p.K,
                                p.B, Kd, p.chunk_s, gc, st, "milnce backward transposed block");
     if (rc) return rc;
     // dtext (n*K, D) = G^T . V   : A = Gt (n*K, P*B), Bm = Vt (D, P*B)
@@ -927,38 +968,39 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
     int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
-    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const Operands o = operands(p, video, text, ws);
+    const __half *vk = o.vk, *tk = o.tk;
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
-    rc = launch_stats2(p.cg, &sc->inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * p.ld_vk,
-                       p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
+    rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * o.ld_vk,
+                       o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)", o.fmt_s);
     if (rc) return rc;
     const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr};
     merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, 1, p.n, p.nb_r, 0, row_lse + p.i0,
                                                             none);
     merge_partials_kernel<<<(p.B + 31) / 32, 1024, 0, st>>>(nullptr, pc, p.K / p.cg, p.B, 0, p.nb_cl, col_part,
                                                             none);
+    b200::note_launches(2);
     B200_LAUNCH_OK("milnce shard finalize");
     return 0;
 }
 
 int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
                         const float *den, const float *nom, const float *grad_loss, void *dvideo,
-                        int grad_bf16, float *dtext_partial, int parts, int reuse, uint8_t *ws,
+                        int grad_bf16, void *dtext_partial, int dtext_bf16, int parts, int reuse, uint8_t *ws,
                         cudaStream_t st) {
     // parts: 1 = G and the partial dtext, 2 = dvideo (from the G a parts-1 call left in the
     // workspace), 3 = both.  Split calls let the caller start the reduce-scatter of dtext
     // while dvideo is still being computed.
     int rc;
-    const __half *vk = reinterpret_cast<const __half *>(ws + p.off_vk);
-    const __half *tk = reinterpret_cast<const __half *>(ws + p.off_tk);
+    const Operands o = operands(p, video, text, ws);
+    const __half *vk = o.vk, *tk = o.tk;
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     if (parts == 2) {
-        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
-        return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                       "milnce dvideo GEMM (shard)");
+        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
+        return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
+                                                       "milnce dvideo GEMM (shard)", o.fmt_b);
     }
     if (!reuse) {
         rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
@@ -966,18 +1008,18 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     }
     B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
-    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), &sc->inv_ss, fast};
-    rc = launch_epig2(vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, tk, p.ld_tk, p.n, (int)p.BK, p.D, gr,
-                                st, "milnce backward (rows-only shard) G");
+    tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), o.inv_ss, fast};
+    rc = launch_epig2(vk + (size_t)p.i0 * o.ld_vk, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, gr,
+                                st, "milnce backward (rows-only shard) G", o.fmt_s);
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
-    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_video, 0};
-    rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g, p.ld_g, vk + (size_t)p.i0 * p.ld_vk, p.ld_vk, (int)p.BK, p.D, p.n, sd, st,
-                                                "milnce partial dtext GEMM (shard)");
+    tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_video, dtext_bf16};
+    rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g, p.ld_g, vk + (size_t)p.i0 * o.ld_vk, o.ld_vk, (int)p.BK, p.D, p.n, sd, st,
+                                                "milnce partial dtext GEMM (shard)", o.fmt_b);
     if (rc || parts == 1) return rc;
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, &sc->s_text, grad_bf16};
-    return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, p.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                   "milnce dvideo GEMM (shard)");
+    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
+    return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
+                                                   "milnce dvideo GEMM (shard)", o.fmt_b);
 }
 
 int check_shard(const Plan &p, int dtype) {
@@ -1103,13 +1145,15 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
     int rc = b200::check_device();
     if (rc) return rc;
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
-    // a_transposed: bit 0 = A passed as (Kd, M), bit 1 = Bm passed as (Kd, N)
+    // a_transposed: bit 0 = A passed as (Kd, M), bit 1 = Bm passed as (Kd, N), bit 2 = A holds bfloat16,
+    // bit 3 = Bm holds bfloat16
     cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t fmt = ((a_transposed & 4) ? tc::IDESC_A_BF16 : 0u) | ((a_transposed & 8) ? tc::IDESC_B_BF16 : 0u);
     switch (a_transposed & 3) {
-        case 0: return launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
-        case 1: return launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
-        case 2: return launch_gemm2<tc::EpiStore, false, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
-        default: return launch_gemm2<tc::EpiStore, true, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook");
+        case 0: return launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);
+        case 1: return launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);
+        case 2: return launch_gemm2<tc::EpiStore, false, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);
+        default: return launch_gemm2<tc::EpiStore, true, true, false, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);
     }
 }
 
@@ -1144,13 +1188,14 @@ extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *
     int rc = b200::check_device();
     if (rc) return rc;
     shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(gathered, W, b, W * b, den, nom, loss);
+    b200::note_launches(1);
     B200_LAUNCH_OK("milnce_shard_combine");
     return 0;
 }
 
 extern "C" int milnce_backward_shard(const void *video, const void *text, const float *den,
                                      const float *nom, const float *grad_loss, void *dvideo,
-                                     int dvideo_dtype, float *dtext_partial, int parts, int B, int K, int D,
+                                     int dvideo_dtype, void *dtext_partial, int dtext_dtype, int parts, int B, int K, int D,
                                      int dtype, int i0, int n, int reuse_forward_ws, void *workspace,
                                      size_t workspace_bytes, void *stream) {
     Plan p;
@@ -1158,8 +1203,9 @@ extern "C" int milnce_backward_shard(const void *video, const void *text, const 
         b200::set_error("milnce_backward_shard: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
         return B200HEAD_ERR_ARG;
     }
-    if (parts < 1 || parts > 3 || (dvideo_dtype != B200HEAD_F32 && dvideo_dtype != B200HEAD_BF16)) {
-        b200::set_error("milnce_backward_shard: parts must be 1, 2 or 3 and dvideo_dtype F32 or BF16");
+    if (parts < 1 || parts > 3 || (dvideo_dtype != B200HEAD_F32 && dvideo_dtype != B200HEAD_BF16) ||
+        (dtext_dtype != B200HEAD_F32 && dtext_dtype != B200HEAD_BF16)) {
+        b200::set_error("milnce_backward_shard: parts must be 1, 2 or 3 and dvideo_dtype / dtext_dtype F32 or BF16");
         return B200HEAD_ERR_ARG;
     }
     if (!video || !text || !den || !nom || !grad_loss || ((parts & 2) && !dvideo) ||
@@ -1174,6 +1220,7 @@ extern "C" int milnce_backward_shard(const void *video, const void *text, const 
     rc = check_common(p, workspace, workspace_bytes);
     if (rc) return rc;
     return backward_shard_impl(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text, den, nom,
-                               grad_loss, dvideo, dvideo_dtype == B200HEAD_BF16 ? 1 : 0, dtext_partial, parts,
+                               grad_loss, dvideo, dvideo_dtype == B200HEAD_BF16 ? 1 : 0, dtext_partial,
+                               dtext_dtype == B200HEAD_BF16 ? 1 : 0, parts,
                                reuse_forward_ws, (uint8_t *)workspace, (cudaStream_t)stream);
 }

@@ -33,7 +33,7 @@ struct AuxPlan {
     // cell (N+M-1, N) float4 per pair, diagonal-major: {w_diag, w_up, w_left, D}
     // acoef (B,N,M): GEMM coefficient of the input gradient, scoef (B,N,M): summand of the
     // "own vector" coefficient; nx (B,N), ny (B,M) norms; rsum (B,N), csum (B,M)
-    size_t off_cell, off_d, off_acoef, off_nx, off_ny, off_rsum, off_csum, total;
+    size_t off_cell, off_d, off_acoef, off_nx, off_ny, off_rsum, off_csum, off_flag, total;
 };
 
 AuxPlan make_aux(int B, int N, int M) {
@@ -47,6 +47,7 @@ AuxPlan make_aux(int B, int N, int M) {
     a.off_ny = take((size_t)B * M * 4);
     a.off_rsum = take((size_t)B * N * 4);
     a.off_csum = take((size_t)B * M * 4);
+    a.off_flag = take(256);  // int: the fused forward could not represent this batch (see fused::WE_LIMIT)
     a.total = o;
     return a;
 }
@@ -60,7 +61,10 @@ constexpr int DK = 32;   // feature chunk
 template <int KIND>
 __global__ void __launch_bounds__(256)
 dist_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int M, int d,
-            float *__restrict__ Dout, float *__restrict__ nx_out, float *__restrict__ ny_out) {
+            float *__restrict__ Dout, float *__restrict__ nx_out, float *__restrict__ ny_out,
+            const int *__restrict__ run_if) {
+    // run_if: device flag; the grid exits at once when it is 0 (the fused kernel handled the batch)
+    if (run_if != nullptr && *run_if == 0) return;
     __shared__ float xs[DK][DT + 4];
     __shared__ float ys[DK][DT + 4];
     __shared__ float snx[DT], sny[DT];
@@ -75,7 +79,7 @@ dist_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int
     // loader mapping: 64 rows x 32 features = 512 float4; two per thread
     const int lr = tid >> 3;          // 0..31 (+32)
     const int lc = (tid & 7) * 4;     // feature offset within the chunk
-    const bool vec_ok = (d % 4 == 0);
+    const bool vec_ok = (d % 4 == 0) && ((((uintptr_t)x | (uintptr_t)y) & 15) == 0);
     for (int k0 = 0; k0 < d; k0 += DK) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -171,7 +175,8 @@ dist_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int
 // thread i owns row i (0-based); at step p it handles column j = p - i.
 __global__ void dp_fwd_kernel(const float *__restrict__ D, int N, int M, float gamma, float bandwidth,
                               float *__restrict__ Rout, float *__restrict__ out,
-                              float4 *__restrict__ cell) {
+                              float4 *__restrict__ cell, const int *__restrict__ run_if) {
+    if (run_if != nullptr && *run_if == 0) return;  // see dist_kernel
     extern __shared__ double sh_up[];  // [2][blockDim.x + 1]
     const int b = blockIdx.x, i = threadIdx.x, T = blockDim.x;
     double *buf0 = sh_up, *buf1 = sh_up + (T + 1);
@@ -381,6 +386,30 @@ grad_kernel(const float *__restrict__ acoef, long long sr, long long sq, int R, 
     }
 }
 
+// dist_kernel + dp_fwd_kernel: the path for any shape and distance.  run_if (device int, may be
+// null): when given and zero, both grids exit immediately.
+int general_forward(const float *x, const float *y, int B, int N, int M, int d, float gamma, float bandwidth,
+                    int dist_kind, float *R, float *out, float *Dm, float *nx, float *ny, float4 *cell,
+                    const int *run_if, cudaStream_t st, const char *who) {
+    dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
+    if (dist_kind == B200HEAD_DIST_COSINE)
+        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+    else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT)
+        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+    else
+        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+    const int T = std::max(32, (N + 31) / 32 * 32);
+    const size_t sh = 2 * (size_t)(T + 1) * sizeof(double);
+    dp_fwd_kernel<<<B, T, sh, st>>>(Dm, N, M, gamma, bandwidth, R, out, cell, run_if);
+    b200::note_launches(2);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        b200::set_error("%s: launch of the distance / wavefront kernels failed: %s", who, cudaGetErrorString(e));
+        return B200HEAD_ERR_CUDA;
+    }
+    return 0;
+}
+
 int check_args(const char *who, const void *x, const void *y, int B, int N, int M, int d, float gamma,
                int dist_kind) {
     if (!x || !y) {
@@ -439,38 +468,36 @@ extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M,
     float *Dm = reinterpret_cast<float *>(ax + a.off_d);
     float *nx = reinterpret_cast<float *>(ax + a.off_nx);
     float *ny = reinterpret_cast<float *>(ax + a.off_ny);
-    if (fused::eligible(N, M, d, dist_kind)) {
+    int *flag = reinterpret_cast<int *>(ax + a.off_flag);
+    const int *run_if = nullptr;
+    if (fused::eligible(N, M, d, dist_kind, gamma, x, y)) {
         // short sequences: one fused kernel per pair (tensor-core distance tile + wavefront)
         float4 *cellp = reinterpret_cast<float4 *>(ax + a.off_cell);
         const int smem = (int)sizeof(fused::FwdSmem);
         if (dist_kind == B200HEAD_DIST_COSINE) {
+            // exp(1 - cos) is bounded: eligible() has already checked gamma, no device-side guard needed
             B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<0>,
                                               cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
             fused::fwd_kernel<0><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
-                                                       nx, ny);
-        } else {
-            B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<1>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            fused::fwd_kernel<1><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
-                                                       nx, ny);
-        }
+                                                       nx, ny, nullptr);
+            b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused forward kernel");
-        return 0;
+            return 0;
+        }
+        // negative_dot distances are unbounded: the kernel raises `flag` when |D| / gamma is beyond its
+        // scaled-pair exponents, and the general kernels below then redo the batch (they exit at
+        // once when the flag is clear)
+        B200_CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), st));
+        B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<1>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        fused::fwd_kernel<1><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
+                                                   nx, ny, flag);
+        b200::note_launches(1);
+        B200_LAUNCH_OK("sdtw fused forward kernel");
+        run_if = flag;
     }
-    dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
-    if (dist_kind == B200HEAD_DIST_COSINE)
-        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT)
-        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    else
-        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    B200_LAUNCH_OK("sdtw dist_kernel");
-    const int T = std::max(32, (N + 31) / 32 * 32);
-    const size_t sh = 2 * (size_t)(T + 1) * sizeof(double);
-    dp_fwd_kernel<<<B, T, sh, st>>>(Dm, N, M, gamma, bandwidth, R, out,
-                                    reinterpret_cast<float4 *>(ax + a.off_cell));
-    B200_LAUNCH_OK("sdtw dp_fwd_kernel");
-    return 0;
+    return general_forward(x, y, B, N, M, d, gamma, bandwidth, dist_kind, R, out, Dm, nx, ny,
+                           reinterpret_cast<float4 *>(ax + a.off_cell), run_if, st, "sdtw_forward");
 }
 
 extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_out, int B, int N,
@@ -497,7 +524,7 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     float *ny = reinterpret_cast<float *>(ax + a.off_ny);
     float *rsum = reinterpret_cast<float *>(ax + a.off_rsum);
     float *csum = reinterpret_cast<float *>(ax + a.off_csum);
-    if (fused::eligible(N, M, d, dist_kind)) {
+    if (fused::eligible(N, M, d, dist_kind, gamma, x, y)) {
         const int smem = (int)sizeof(fused::BwdSmem);
         if (dist_kind == B200HEAD_DIST_COSINE) {
             B200_CUDA_OK(cudaFuncSetAttribute(fused::bwd_kernel<0>,
@@ -510,6 +537,7 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
             fused::bwd_kernel<1><<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E,
                                                        dx, dy);
         }
+        b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused backward kernel");
         return 0;
     }
@@ -526,6 +554,7 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT) SDTW_BWD(B200HEAD_DIST_NEGATIVE_DOT);
     else SDTW_BWD(B200HEAD_DIST_EUCLIDEAN);
 #undef SDTW_BWD
+    b200::note_launches(3);
     B200_LAUNCH_OK("sdtw backward kernels");
     (void)gamma;
     return 0;
@@ -619,20 +648,8 @@ extern "C" int sdtw_forward_noalloc(const float *x, const float *y, int B, int N
     float *Dm = reinterpret_cast<float *>(sx + off_d);
     float *nx = reinterpret_cast<float *>(sx + off_nx);
     float *ny = reinterpret_cast<float *>(sx + off_ny);
-    cudaStream_t st = (cudaStream_t)stream;
-    dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
-    if (dist_kind == B200HEAD_DIST_COSINE)
-        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT)
-        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    else
-        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny);
-    B200_LAUNCH_OK("sdtw_forward_noalloc dist_kernel");
-    const int T = std::max(32, (N + 31) / 32 * 32);
-    const size_t sh = 2 * (size_t)(T + 1) * sizeof(double);
-    dp_fwd_kernel<<<B, T, sh, st>>>(Dm, N, M, gamma, bandwidth, R, out, nullptr);
-    B200_LAUNCH_OK("sdtw_forward_noalloc dp_fwd_kernel");
-    return 0;
+    return general_forward(x, y, B, N, M, d, gamma, bandwidth, dist_kind, R, out, Dm, nx, ny, nullptr, nullptr,
+                           (cudaStream_t)stream, "sdtw_forward_noalloc");
 }
 
 #ifdef SDTW_PROFILE

@@ -142,7 +142,12 @@ __device__ __forceinline__ void spin_pause() {
 // exponent (f = 0 encodes P = 0, i.e. R = +inf).  fp32 significands lose ~1e-7 per
 // step relative, i.e. ~1e-6 * gamma absolute on R; the soft-min weights saved for the
 // backward are ratios of neighbouring P and need no large-number subtraction at all.
-constexpr int E_ZERO = -(1 << 28);
+// The exponent of P = 0 is a sentinel far below every real exponent: the kernels keep real
+// exponents inside (-2^29, 2^29) (a cell weight's exponent is bounded by WE_LIMIT, a path has at
+// most 127 cells; the host and the tile phase enforce it, see fused::eligible and `overflow`), so
+// a real exponent never meets the sentinel and `e - emax` never leaves the int range.
+constexpr int E_ZERO = -(1 << 30);
+constexpr double WE_LIMIT = 4194304.0;  // 2^22: |floor(-D log2(e) / gamma)| allowed per cell
 __device__ __forceinline__ float pow2_nonpos(int k) {  // 2^k for k <= 0, flushing to 0 below 2^-126
     k = max(k, -127);
     return __int_as_float((k + 127) << 23);
@@ -184,7 +189,8 @@ template <int KIND>
 __global__ void __launch_bounds__(256, 2)
 fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int M, int d, float gamma,
            float bandwidth, float *__restrict__ Rout, float *__restrict__ out,
-           float4 *__restrict__ cell, float *__restrict__ nx_out, float *__restrict__ ny_out) {
+           float4 *__restrict__ cell, float *__restrict__ nx_out, float *__restrict__ ny_out,
+           int *__restrict__ overflow) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     FwdSmem &s = *reinterpret_cast<FwdSmem *>(smem_raw);
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -259,6 +265,7 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
     __syncthreads();
     // distance tile and per-cell weight exp(-D/gamma) as mantissa/exponent
     const double inv_g2 = 1.4426950408889634 / (double)gamma;  // log2(e) / gamma
+    bool too_big = false;  // |D| / gamma beyond what the scaled-pair exponents can carry
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
@@ -275,6 +282,7 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
             s.Dt[i][j] = v;
             const double xx = -(double)v * inv_g2;
             const double fl = floor(xx);
+            if (i < N && j < M && !(fabs(fl) <= WE_LIMIT)) too_big = true;  // (also catches NaN)
             s.We[i][j] = (int)fl;
             // a Sakoe-Chiba-pruned cell (soft_dtw_cuda.py:60) gets weight 0: the wavefront then needs no
             // per-step bandwidth test, P = sum * 0 = 0 marks the cell unreachable
@@ -285,6 +293,8 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
         if (tid < 64) { if (tid < N) nx_out[(size_t)b * N + tid] = s.nx[tid]; }
         else { if (tid - 64 < M) ny_out[(size_t)b * M + tid - 64] = s.ny[tid - 64]; }
     }
+    // the host then re-runs the batch on the float64 general path (sdtw_forward)
+    if (too_big && overflow != nullptr) *overflow = 1;
     for (int e = tid; e < 2 * T; e += 256) s.mb[e] = MB_EMPTY;
     // border of R as the reference initialises it (soft_dtw_cuda.py:135-136)
     float *Rb = Rout ? Rout + (size_t)b * (N + 2) * (M + 2) : nullptr;
@@ -658,9 +668,16 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
     SDTW_STAMP(11);
 }
 
-// the general path covers everything else
-__host__ inline bool eligible(int N, int M, int d, int dist_kind) {
-    return N <= T && M <= T && (d % 4 == 0) && dist_kind != 2;
+// The general path covers everything else.  gamma: the cosine distance exp(1 - cos) lies in
+// [1, e^2], so 127 cells of at most e^2 log2(e) / gamma each stay below 2^29 for gamma >= 3e-6
+// (decided here); negative_dot distances are unbounded, so its tile phase checks every cell against
+// WE_LIMIT and raises the `overflow` flag that makes sdtw_forward redo the batch on the general path.
+// x, y: the loaders issue 16-byte cp.async.
+__host__ inline bool eligible(int N, int M, int d, int dist_kind, float gamma, const void *x, const void *y) {
+    if (!(N <= T && M <= T && (d % 4 == 0) && dist_kind != 2)) return false;
+    if ((((uintptr_t)x | (uintptr_t)y) & 15) != 0) return false;
+    if (dist_kind == 0 && !(gamma >= 3e-6f)) return false;
+    return true;
 }
 
 }  // namespace fused

@@ -506,7 +506,7 @@ struct EpiRowColT {
     };
     __device__ static Consts load_consts(const Params &p) {
         Consts k;
-        k.sc = __ldg(p.scale_dev) * LOG2E;  // log2 domain
+        k.sc = (p.scale_dev ? __ldg(p.scale_dev) : 1.f) * LOG2E;  // log2 domain; null: operands are unscaled
         return k;
     }
     __device__ static Pre preload(const Params &, const EpiCtx &, int, int, bool) { return Pre{}; }
@@ -778,7 +778,7 @@ struct EpiG {
         Consts k;
         k.fast = __ldg(p.fast.flag_dev) != 0;
         k.mid = __ldg(p.fast.mid_log2_dev);
-        k.sc = __ldg(p.scale_dev) * LOG2E;
+        k.sc = (p.scale_dev ? __ldg(p.scale_dev) : 1.f) * LOG2E;
         return k;
     }
     __device__ static void begin_tile(const Params &p, const EpiCtx &c, const Pre &q, const Consts &k, Tile &t,
@@ -897,7 +897,13 @@ struct GemmShape {
     // kr % a_plane_rows, column offset (kr / a_plane_rows) * a_plane_cols.  0 = one plane.
     // (a_plane_rows must be a multiple of BLOCK_K.)
     int a_plane_rows, a_plane_cols;
+    // OR-ed into the instruction descriptor (CTA-pair kernels): IDESC_A_BF16 / IDESC_B_BF16 make the
+    // tensor core read that operand as bfloat16 instead of float16.  The two formats are independent,
+    // which is how the gradient GEMMs multiply the fp16 gradient tiles by the caller's bf16 embeddings
+    // without a staged fp16 copy of them.
+    uint32_t idesc_or;
 };
+constexpr uint32_t IDESC_A_BF16 = 1u << 7, IDESC_B_BF16 = 1u << 10;
 
 // threads per CTA: TMA warp + MMA warp + 4 * PARTS epilogue warps
 template <class Epi>

@@ -233,7 +233,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA; the warp runs convergent, one lane issues) ====
         if (rank == 0) {
-            constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            const uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, A_MN ? 1 : 0, B_MN ? 1 : 0) | shape.idesc_or;
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0;
@@ -496,7 +496,7 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA; convergent warp, one lane issues) =====
         if (rank == 0) {
-            constexpr uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, 0);
+            const uint32_t idesc = make_idesc_f16(PAIR_M, PAIR_N, 0) | shape.idesc_or;
             int stage = 0;
             uint32_t phase = 0;
             uint32_t cc = 0, a_gen = 0;

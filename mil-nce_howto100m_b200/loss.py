@@ -115,8 +115,9 @@ class CudaBackend:
         return den, nom, loss.reshape(())
 
     @staticmethod
-    def backward_shard(video, text, den, nom, grad_loss, i0, n, ws, parts=3, grad_dtype=torch.float32):
-        """Returns (dvideo (n, D) in grad_dtype or None, dtext_partial (B*K, D) float32 or None).
+    def backward_shard(video, text, den, nom, grad_loss, i0, n, ws, parts=3, grad_dtype=torch.float32,
+                       partial_dtype=torch.float32):
+        """Returns (dvideo (n, D) in grad_dtype or None, dtext_partial (B*K, D) in partial_dtype or None).
 
         parts=1: gradient tiles + dtext_partial only; parts=2: dvideo only, from the workspace a
         parts=1 call left; parts=3: both.  dtext_partial is to be reduce-scattered."""
@@ -133,13 +134,14 @@ class CudaBackend:
             ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
             reuse = 0
         dv = torch.empty(n, D, dtype=grad_dtype, device=dev) if parts & 2 else None
-        dtp = torch.empty(B * K, D, dtype=torch.float32, device=dev) if parts & 1 else None
+        dtp = torch.empty(B * K, D, dtype=partial_dtype, device=dev) if parts & 1 else None
         gcode = 0 if grad_dtype == torch.float32 else 1
+        pcode = 0 if partial_dtype == torch.float32 else 1
         null = ctypes.c_void_p(0)
         with torch.cuda.device(dev):
             rc = lib.milnce_backward_shard(_ptr(video), _ptr(text), _ptr(den), _ptr(nom), _ptr(grad_loss),
                                            _ptr(dv) if dv is not None else null, gcode,
-                                           _ptr(dtp) if dtp is not None else null, parts,
+                                           _ptr(dtp) if dtp is not None else null, pcode, parts,
                                            B, K, D, code, i0, n, reuse, _ptr(ws), ws.numel(),
                                            _lib.stream_ptr(dev))
         _lib.check(rc, "milnce_backward_shard")

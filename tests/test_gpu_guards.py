@@ -42,7 +42,10 @@ def _p(t):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("B,K,D", [(300, 4, 136), (129, 3, 72), (64, 1, 8), (520, 2, 264)])
+# (64, 4, 100) and (96, 2, 36): D not a multiple of 8 - bf16 inputs then leave the vectorised staging
+# kernels for the generic ones (which once wrote transposed copies the one-plane layout has no room for)
+@pytest.mark.parametrize("B,K,D", [(300, 4, 136), (129, 3, 72), (64, 1, 8), (520, 2, 264), (64, 4, 100),
+                                   (96, 2, 36)])
 def test_milnce_stays_inside_its_buffers(B, K, D, dtype):
     lib = _lib.load()
     code = _lib.BF16 if dtype == torch.bfloat16 else _lib.F32

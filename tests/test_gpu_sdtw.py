@@ -166,3 +166,62 @@ def test_linearity_in_grad_out():
     dx2, dy2, _ = sdtw_backward_raw(x, y, 3.0 * g1, 0.1, 0.0, KINDS["cosine"], aux)
     assert ((dx2 - 3.0 * dx1).norm() / dx2.norm()).item() < 1e-6
     assert ((dy2 - 3.0 * dy1).norm() / dy2.norm()).item() < 1e-6
+
+
+def _forward_only(x, y, gamma, dist):
+    out, R, _ = sdtw_forward_raw(x.cuda(), y.cuda(), gamma, 0.0, KINDS[dist], want_R=True)
+    torch.cuda.synchronize()
+    D = sdtw_oracle.dist_forward(x.double().numpy(), y.double().numpy(), dist)
+    Rref = sdtw_oracle.dp_forward(D, float(np.float32(gamma)), 0.0)
+    Rg = R.cpu().numpy().astype(np.float64)
+    assert np.array_equal(np.isinf(Rg), np.isinf(Rref)), "inf pattern of R differs"
+    fin = np.isfinite(Rref)
+    e_R = np.max(np.abs(Rg[fin] - Rref[fin])) / np.max(np.abs(Rref[fin]))
+    e_out = rel_err(out.cpu().numpy(), Rref[:, -2, -2])
+    print(f"{dist} gamma={gamma}: R {e_R:.2e} out {e_out:.2e}")
+    return e_R, e_out
+
+
+@pytest.mark.parametrize("gamma", [1e-4, 1e-5, 1e-6])
+def test_tiny_gamma_cosine_short_sequences(gamma):
+    """N, M <= 64 with the gamma the reference's CDTW uses (1e-5, loss.py:74) and below: the per-pair
+    kernel's scaled-pair exponents reach ~1e8 here and must neither meet the 'zero' sentinel nor
+    leave the int range (gamma = 1e-6 is sent to the float64 general path by the host)."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(4, 64, 32, generator=g)
+    y = torch.randn(4, 64, 32, generator=g)
+    e_R, e_out = _forward_only(x, y, gamma, "cosine")
+    assert max(e_R, e_out) < 1e-5
+
+
+def test_negative_dot_beyond_the_short_kernel_range_falls_back_on_the_device():
+    """|D| / gamma too large for the per-pair kernel's exponents (dots of tens at gamma = 1e-5): it
+    raises its flag and the general kernels redo the batch in the same sdtw_forward call; a second
+    call with benign values on the same aux must take the fast kernel again (flag cleared)."""
+    g = torch.Generator().manual_seed(12)
+    x = torch.randn(3, 48, 512, generator=g)
+    y = torch.randn(3, 40, 512, generator=g)
+    e_R, e_out = _forward_only(x, y, 1e-5, "negative_dot")
+    assert max(e_R, e_out) < 1e-5
+    _compare(x * 0.05, y * 0.05, 0.1, None, "negative_dot", name="after-fallback")
+
+
+def test_unaligned_inputs_take_the_scalar_loaders():
+    """A (B, N, d) view that starts 4 bytes into its storage is contiguous but not 16-byte aligned:
+    it must be served (general path, scalar loads), not fault."""
+    g = torch.Generator().manual_seed(13)
+    B, N, M, d = 3, 24, 20, 16
+    bx = torch.randn(B * N * d + 1, generator=g).cuda()
+    by = torch.randn(B * M * d + 1, generator=g).cuda()
+    x = bx[1:].view(B, N, d)
+    y = by[1:].view(B, M, d)
+    assert x.data_ptr() % 16 != 0 and x.is_contiguous()
+    out, R, aux = sdtw_forward_raw(x, y, 0.5, 0.0, KINDS["cosine"], want_R=True)
+    dx, dy, _ = sdtw_backward_raw(x, y, torch.ones(B, device="cuda"), 0.5, 0.0, KINDS["cosine"], aux)
+    xa, ya = x.clone(), y.clone()
+    out2, R2, aux2 = sdtw_forward_raw(xa, ya, 0.5, 0.0, KINDS["cosine"], want_R=True)
+    dx2, dy2, _ = sdtw_backward_raw(xa, ya, torch.ones(B, device="cuda"), 0.5, 0.0, KINDS["cosine"], aux2)
+    torch.cuda.synchronize()
+    assert rel_err(out.cpu().numpy(), out2.cpu().numpy()) < 1e-5
+    assert rel_err(dx.cpu().numpy(), dx2.cpu().numpy()) < 1e-5
+    assert rel_err(dy.cpu().numpy(), dy2.cpu().numpy()) < 1e-5

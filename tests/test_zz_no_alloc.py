@@ -6,11 +6,17 @@ already owns the whole GPU, or a loop that must not pay the device-wide stall of
 cudaMalloc/cudaFree.  For them the library carries its own 8 MiB scratch buffer.
 
 The entry point is driven through the C ABI (ctypes) and compared with the regular
-sdtw_forward entry point (caller-allocated aux) on two consecutive calls.  The
-second call is smaller than the first, so it runs on top of the first call's
-leftovers in the shared buffer - the results must not depend on them.  Tolerance:
-1e-5 relative, the same as the other soft-DTW tests (the kernels are the same, so
-the match is expected to be exact).  This file is named to be collected last.
+sdtw_forward entry point (caller-allocated aux) on consecutive calls.  Later calls are
+smaller than the first, so they run on top of the first call's leftovers in the shared
+buffer - the results must not depend on them.  Tolerance: 1e-5 relative, the same as the
+other soft-DTW tests.  What the comparison means depends on the shape:
+  * 256 x (64 x 64) x 512, cosine: the regular entry point takes the fused per-pair
+    kernel there while the no-alloc one always runs the distance + wavefront kernels of
+    the general path, so this is a cross-check between two kernel families (1e-5);
+  * shapes the fused kernel does not cover (N = 80, or euclidean): both entry points run
+    the very same kernels, and the outputs must be bit-identical.
+The first call is also checked against the CPU oracle directly.  This file is named to be
+collected last.
 """
 import ctypes
 
@@ -66,12 +72,36 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     # call 2: smaller, ragged and pruned, straight after - reuses the dirty buffer
     x2 = torch.randn(5, 37, 24, generator=g).cuda()
     y2 = torch.randn(5, 41, 24, generator=g).cuda()
-    calls = [(x1, y1, 0.1, 0.0, KINDS["cosine"]), (x2, y2, 1.0, 6.0, KINDS["negative_dot"])]
-    got = [_noalloc(*c) for c in calls]        # two calls in a row, nothing in between
+    # call 3: longer than the fused kernels' 64 frames - both entry points run the same kernels
+    x3 = torch.randn(6, 80, 32, generator=g).cuda()
+    y3 = torch.randn(6, 72, 32, generator=g).cuda()
+    calls = [(x1, y1, 0.1, 0.0, KINDS["cosine"]), (x2, y2, 1.0, 6.0, KINDS["negative_dot"]),
+             (x3, y3, 0.5, 0.0, KINDS["cosine"])]
+    got = [_noalloc(*c) for c in calls]        # calls in a row, nothing in between
     for c, (out, R) in zip(calls, got):
         ref_out, ref_R = _regular(*c)
         assert _same(out, ref_out) < 1e-5
         assert _same(R, ref_R) < 1e-5
+    # same kernels on both sides: bit-identical
+    out3, R3 = got[2]
+    ref_out3, ref_R3 = _regular(*calls[2])
+    assert torch.equal(out3, ref_out3) and torch.equal(R3, ref_R3)
+    # and the first call against the CPU oracle itself (float64 recurrence, soft_dtw_cuda.py:185-206)
+    from oracle import sdtw_oracle
+    sub = slice(0, 16)
+    D = sdtw_oracle.dist_forward(x1[sub].double().cpu().numpy(), y1[sub].double().cpu().numpy(), "cosine")
+    Rref = sdtw_oracle.dp_forward(D, float(np.float32(0.1)), 0.0)
+    assert rel_err(got[0][0][sub].cpu().numpy(), Rref[:, -2, -2]) < 1e-5
+
+
+def test_noalloc_euclidean_is_bit_identical_to_regular():
+    """euclidean never takes the fused kernel: the two entry points run the same code."""
+    g = torch.Generator().manual_seed(7)
+    x = (torch.randn(9, 33, 20, generator=g) * 0.3).cuda()
+    y = (torch.randn(9, 29, 20, generator=g) * 0.3).cuda()
+    out, R = _noalloc(x, y, 0.7, 0.0, KINDS["euclidean"])
+    ref_out, ref_R = _regular(x, y, 0.7, 0.0, KINDS["euclidean"])
+    assert torch.equal(out, ref_out) and torch.equal(R, ref_R)
 
 
 def test_noalloc_rejects_sizes_beyond_the_builtin_buffer():
