@@ -6,17 +6,21 @@
 Headline metric: MIL-NCE forward+backward similarity-pairs/s at global batch
 B=8192, K=4, D=512 (BASELINE.json configs[1]; pairs per step = B * B*K).  One
 "step" = one forward + one backward of the loss on one batch of synthetic
-embeddings.  At N > 1 GPUs the global batch is sharded over ranks (configs[3]),
-embeddings are all-gathered with NCCL, each rank computes only its rows of the
-similarity matrix and the text gradient is reduce-scattered (strong scaling: total
-work fixed).
+embeddings.  At N > 1 GPUs the global batch is sharded over ranks (configs[3]):
+embeddings are all-gathered with NCCL and every rank computes its share of the
+similarity matrix (strong scaling: total work fixed); rank 0 first checks the
+sharded loss and its gradient slices against the single-GPU module.
 
 One JSON line is printed by rank 0.  Besides the contract keys it carries
-  roofline      tensor-pipe roofline of the step (algorithmic 6*B*BK*D FLOP)
-  cpu_baseline  the oracle's torch port of the reference loss timed on host cores
-  sdtw          the soft-DTW half of the metric (DP cells/s, HBM roofline)
---impl reference times the reference's CPU path (oracle port; the reference is
-pure Python and /root/reference does not exist on the GPU box).
+  roofline            tensor-pipe roofline of the timed region; its peak is the burst or the
+                      sustained cuBLAS figure of MEASURED_PEAKS.json, whichever regime the clocks
+                      sampled during the region show
+  roofline_sustained  the same over a >= 2 s run against the sustained peak (N = 1)
+  e2e                 pinned-host inputs in, loss out, through the module API
+  cpu_baseline        the reference's own loss.py on the box's host cores (oracle/_ref), else the port
+  sdtw                the soft-DTW half of the metric: DP cells/s, HBM roofline, e2e, CPU baseline;
+                      at N > 1 every rank runs its own 256 pairs (independent units, weak scaling)
+--impl reference times the reference's CPU path on the same config with all host threads.
 """
 from __future__ import annotations
 
@@ -48,10 +52,12 @@ def parse():
     ap.add_argument("--candidates", type=int, default=4)
     ap.add_argument("--dim", type=int, default=512)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--cpu-sample-batch", type=int, default=2048)
+    ap.add_argument("--scheme", default="auto", choices=["auto", "rows", "rowcol"])
     ap.add_argument("--no-sdtw", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-graph", action="store_true", help="e2e leg through the eager module instead of the CUDA graph")
+    ap.add_argument("--no-graph", action="store_true", help="time the eager module instead of the CUDA graph")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s sustained-regime leg")
+    ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="wall-clock budget of the reference arm")
     return ap.parse_args()
 
 
@@ -60,8 +66,8 @@ def peaks():
     if os.path.exists(p):
         d = json.load(open(p))
         return {"hbm": d["hbm_gbs"], "bf16_burst": d["bf16_tflops"],
-                "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
-    return {"hbm": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "src": "fallback"}
+                "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "MEASURED_PEAKS.json"}
+    return {"hbm": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "src": "B200_PROFILING.md fallback"}
 
 
 class ClockSampler:
@@ -111,27 +117,77 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------
-# reference arm / CPU baseline: the oracle's torch port of loss.py:10-18 on host cores
+# reference arm / CPU baselines: the reference's own modules (oracle/_ref) on host cores,
+# the oracle's port when they are not on this box
 # ----------------------------------------------------------------------------
-def cpu_milnce(batch, K, D, steps, warmup):
-    from oracle import milnce_oracle
+def host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm is to use every core it can."""
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0)) or n
+    except Exception:
+        pass
+    torch.set_num_threads(n)
+    return n
+
+
+def cpu_milnce(batch, K, D, steps, warmup, budget_s):
+    """fp32 MILNCELoss forward+backward on the host.  Returns (pairs/s, s/step, steps, warmup, kind)."""
+    from oracle import milnce_oracle, ref_loader
+    kind = "port"
+    fn = milnce_oracle.milnce_torch_port
+    shim = None
+    if not ref_loader.why_unavailable():
+        mod = ref_loader.load("loss").MILNCELoss()   # loss.py:6-18, unmodified
+        fn = lambda v, t: mod(v, t)
+        shim = ref_loader.cpu_cuda_shim
+        kind = "reference"
     torch.manual_seed(0)
     v = (torch.randn(batch, D) * 0.05).requires_grad_(True)
     t = (torch.randn(batch * K, D) * 0.05).requires_grad_(True)
-    times = []
-    for i in range(warmup + steps):
+
+    def one():
         t0 = time.perf_counter()
-        loss = milnce_oracle.milnce_torch_port(v, t)
+        if shim is not None:
+            with shim():
+                loss = fn(v, t)
+        else:
+            loss = fn(v, t)
         loss.backward()
         v.grad = None
         t.grad = None
-        if i >= warmup:
-            times.append(time.perf_counter() - t0)
+        return time.perf_counter() - t0
+
+    t_start = time.perf_counter()
+    first = one()
+    warm_done = 1
+    while warm_done < warmup and (time.perf_counter() - t_start) + first * 2 < budget_s * 0.25:
+        one()
+        warm_done += 1
+    times = []
+    while len(times) < steps:
+        times.append(one())
+        if (time.perf_counter() - t_start) + times[-1] > budget_s:
+            break
     sec = sum(times) / len(times)
-    return batch * batch * K / sec, sec
+    return batch * batch * K / sec, sec, len(times), warm_done, kind
 
 
 def cpu_sdtw(pairs, N, M, d):
+    """SoftDTW(gamma=0.1, cosine) forward+backward on the host.  Returns (cells/s, seconds, kind, note)."""
+    from oracle import ref_loader
+    if not ref_loader.why_unavailable():
+        sd = ref_loader.load("soft_dtw_cuda")
+        mod = sd.SoftDTW(False, 0.1, dist_func="cosine")     # numba-CPU path, soft_dtw_cuda.py:243-271
+        torch.manual_seed(1234)
+        x = torch.randn(pairs, N, d, requires_grad=True)
+        y = torch.randn(pairs, M, d, requires_grad=True)
+        mod(x[:2], y[:2]).sum().backward()                   # numba JIT outside the timed region
+        x.grad = y.grad = None
+        t0 = time.perf_counter()
+        mod(x, y).sum().backward()
+        sec = time.perf_counter() - t0
+        return 2.0 * pairs * N * M / sec, sec, "reference", "soft_dtw_cuda.py numba-CPU path with its torch distance function"
     from oracle import sdtw_oracle
     import numpy as np
     rng = np.random.default_rng(1234)
@@ -141,27 +197,27 @@ def cpu_sdtw(pairs, N, M, d):
     t0 = time.perf_counter()
     sdtw_oracle.softdtw(x, y, gamma=0.1, dist_func="cosine")
     sec = time.perf_counter() - t0
-    return 2.0 * pairs * N * M / sec, sec
+    return 2.0 * pairs * N * M / sec, sec, "port", "oracle (numpy distance + C recurrences)"
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    bs = min(args.cpu_sample_batch, args.batch)
-    steps = max(1, min(args.steps, 8))
-    warm = max(1, min(args.warmup, 2))
-    val, sec = cpu_milnce(bs, args.candidates, args.dim, steps, warm)
-    cores = torch.get_num_threads()
-    sample = (f"B={bs} of {args.batch}, K={args.candidates}, D={args.dim}, fp32, torch CPU port of "
-              f"loss.py:10-18, {steps} steps")
+    cores = host_threads()
+    B, K, D = args.batch, args.candidates, args.dim
+    val, sec, steps, warm, kind = cpu_milnce(B, K, D, args.steps, args.warmup, args.cpu_budget_s)
+    what = "reference loss.py:6-18 (unmodified, .cuda() shimmed to the host)" if kind == "reference" else \
+        "torch port of loss.py:10-18 (oracle/_ref not on this box)"
+    sample = (f"B={B}, K={K}, D={D}, fp32, {what}, {steps} steps after {warm} warm-up "
+              f"(requested {args.steps}/{args.warmup}; capped by a {args.cpu_budget_s:.0f} s budget)")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"MILNCELoss fwd+bwd B={args.batch} K={args.candidates} D={args.dim}",
-                   "sample": sample},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": f"MILNCELoss fwd+bwd B={B} K={K} D={D} (BASELINE configs[1])",
+                   "global_batch": B, "candidates": K, "dim": D, "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -172,12 +228,16 @@ def run_reference(args):
 # our arm
 # ----------------------------------------------------------------------------
 def measured_traffic():
-    """DRAM bytes per step from the committed ncu --set full captures (profiles/r1_traffic.json)."""
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-            return json.load(f)
-    except Exception:
-        return {}
+    """DRAM bytes per step from the committed ncu --set full captures (newest round first)."""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                d = json.load(f)
+                d["_file"] = "profiles/" + name
+                return d
+        except Exception:
+            continue
+    return {}
 
 
 def timed(fn, steps, warmup, barrier):
@@ -193,6 +253,11 @@ def timed(fn, steps, warmup, barrier):
     barrier()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / 1e3  # seconds for `steps` steps
+
+
+def launches():
+    import milnce_b200
+    return int(milnce_b200._lib.load().b200head_launch_count())
 
 
 def run_b200(args):
@@ -227,12 +292,15 @@ def run_b200(args):
     assert B % world == 0, "global batch must divide by the number of GPUs"
     b = B // world
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
-    g = torch.Generator().manual_seed(1000 + rank)
-    v_host = (torch.randn(b, D, generator=g) * 0.05).to(dtype).pin_memory()
-    t_host = (torch.randn(b * K, D, generator=g) * 0.05).to(dtype).pin_memory()
+
+    def shard(r):
+        g = torch.Generator().manual_seed(1000 + r)
+        return ((torch.randn(b, D, generator=g) * 0.05).to(dtype), (torch.randn(b * K, D, generator=g) * 0.05).to(dtype))
+
+    v_host, t_host = (x.pin_memory() for x in shard(rank))
     v_dev = v_host.to(dev).requires_grad_(True)
     t_dev = t_host.to(dev).requires_grad_(True)
-    loss_mod = milnce_b200.GatheredMILNCELoss() if world > 1 else milnce_b200.MILNCELoss()
+    loss_mod = milnce_b200.GatheredMILNCELoss(scheme=args.scheme) if world > 1 else milnce_b200.MILNCELoss()
 
     def step():
         v_dev.grad = None
@@ -241,14 +309,82 @@ def run_b200(args):
         loss.backward()
         return loss
 
-    # e2e: host buffers in, loss out, through the module API.  Double-buffered like a training input
-    # pipeline: step i+1's inputs cross PCIe on a copy stream while step i computes, and every
-    # step's H2D copy and D2H loss read happen inside the timed region.
-    copy_stream = torch.cuda.Stream(device=dev)
+    # ---- N > 1: the sharded result against the single-GPU module, before anything is timed ----
+    parity = None
+    if world > 1:
+        loss_s = step().detach().clone()
+        dv_s, dt_s = v_dev.grad.clone(), t_dev.grad.clone()
+        ok = torch.ones(1, device=dev)
+        if rank == 0:
+            full = [shard(r) for r in range(world)]
+            V = torch.cat([f[0] for f in full]).to(dev).requires_grad_(True)
+            T = torch.cat([f[1] for f in full]).to(dev).requires_grad_(True)
+            ref = milnce_b200.MILNCELoss()(V, T)
+            ref.backward()
+            rel = lambda a, r_: ((a.double() - r_.double()).norm() / r_.double().norm()).item()
+            e = {"loss": abs(loss_s.item() - ref.item()) / abs(ref.item()),
+                 "dvideo": rel(dv_s, V.grad[:b]), "dtext": rel(dt_s, T.grad[:b * K])}
+            gtol = 3e-3 if dtype == torch.bfloat16 else 1e-5
+            passed = e["loss"] < 1e-5 and e["dvideo"] < gtol and e["dtext"] < gtol
+            parity = {"parity_checked": True, "passed": bool(passed), "errors": e,
+                      "tolerance": {"loss": 1e-5, "grad": gtol},
+                      "what": "rank 0: sharded loss and its own gradient slices vs MILNCELoss on the whole batch on one GPU"}
+            del V, T, ref, full
+            torch.cuda.empty_cache()
+            if not passed:
+                ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() == 0:
+            if rank == 0:
+                print(f"bench.py: multi-GPU parity check FAILED: {parity}", file=sys.stderr)
+            sys.exit(3)
+
+    # ---- device-resident leg (`value`) ----
+    # N = 1: forward + backward replayed as one CUDA graph through the package's GraphedMILNCEStep (the
+    # eager module is also timed and reported); N > 1: the eager GatheredMILNCELoss (NCCL inside).
     graphed = world == 1 and not args.no_graph
+    gsteps = []
+    launches_per_replay = None
     if graphed:
-        # one CUDA graph per input slot: forward + backward replayed with a single launch
-        gsteps = [milnce_b200.GraphedMILNCEStep(B, K, D, dtype=dtype, device=dev) for _ in range(2)]
+        n0 = launches()
+        gsteps = [milnce_b200.GraphedMILNCEStep(B, K, D, dtype=dtype, device=dev, warmup=1) for _ in range(2)]
+        launches_per_replay = (launches() - n0) // (2 * 2)   # per instance: one warm-up pass + the capture
+        with torch.no_grad():
+            for gs in gsteps:
+                gs.video.copy_(v_dev)
+                gs.text.copy_(t_dev)
+
+    def step_graph():
+        gsteps[0].replay()
+
+    n0 = launches()
+    with ClockSampler(local) as clk_e:
+        sec_eager = max_over_ranks(timed(step, args.steps, args.warmup, barrier))
+    eager_launches = launches() - n0 - 0
+    eager_launches = eager_launches * args.steps // (args.steps + args.warmup)
+    clocks = clk_e.summary()
+    sec = sec_eager
+    gpu_launches = eager_launches
+    if graphed:
+        with ClockSampler(local) as clk_g:
+            sec = timed(step_graph, args.steps, args.warmup, barrier)
+        clocks = clk_g.summary()
+        gpu_launches = launches_per_replay * args.steps
+
+    # ---- sustained regime: >= 2 s of back-to-back steps (the GPU settles at its power cap) ----
+    sustained = None
+    if world == 1 and not args.no_sustained:
+        per = sec / args.steps
+        n_sus = max(args.steps, int(2.2 / per))
+        with ClockSampler(local) as clk_s:
+            sec_s = timed(step_graph if graphed else step, n_sus, 3, barrier)
+        sustained = (sec_s / n_sus, n_sus, clk_s.summary())
+
+    # ---- e2e: host buffers in, loss out, through the module API.  Double-buffered like a training
+    # input pipeline: step i+1's inputs cross PCIe on a copy stream while step i computes, and
+    # every step's H2D copy and D2H loss read happen inside the timed region.
+    copy_stream = torch.cuda.Stream(device=dev)
+    if graphed:
         bufs = [(gs.video, gs.text) for gs in gsteps]
     else:
         bufs = [(torch.empty_like(v_dev), torch.empty_like(t_dev)) for _ in range(2)]
@@ -285,11 +421,9 @@ def run_b200(args):
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         cur.synchronize()  # the reference's loss.item() (main_distributed.py:241)
 
-    with ClockSampler(local) as clk:
-        sec = max_over_ranks(timed(step, args.steps, args.warmup, barrier))
     sec_e2e = max_over_ranks(timed(step_e2e, args.steps, max(3, args.warmup // 2), barrier))
 
-    # forward / backward split (events on the launching stream)
+    # forward / backward split of the eager module (events on the launching stream)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     fwd_ms = bwd_ms = 0.0
     reps = max(3, args.steps // 4)
@@ -310,7 +444,12 @@ def run_b200(args):
     ms_step = sec / args.steps * 1e3
     flop_alg = 6.0 * B * (B * K) * D  # 3 GEMMs, tile recompute not credited
     achieved = flop_alg / (ms_step * 1e-3) / 1e12
-    peak = pk["bf16_sustained"] * world
+    # the peak of the regime the timed region ran in: a short region without a power cap is a burst
+    capped = "sw_power_cap" in (clocks.get("reasons") or [])
+    burst = (sec < 1.0) and not capped
+    peak1 = pk["bf16_burst"] if burst else pk["bf16_sustained"]
+    peak = peak1 * world
+    traffic = measured_traffic()
     line = {
         "metric": METRIC, "value": pairs * args.steps / sec, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
@@ -318,34 +457,53 @@ def run_b200(args):
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"MILNCELoss fwd+bwd B={B} K={K} D={D} (BASELINE configs[1])",
                    "global_batch": B, "candidates": K, "dim": D,
-                   "parallelism": (f"dp{world}: batch sharded over ranks, NCCL all-gather of the embeddings, each rank "
-                                   f"computes its rows of S, reduce-scatter of the text gradient") if world > 1 else "single GPU",
+                   "launch": ("one CUDA graph replay per step (GraphedMILNCEStep)" if graphed else "eager module calls"),
+                   "parallelism": (f"dp{world}: batch sharded over ranks, scheme={getattr(loss_mod, 'last_scheme', args.scheme)}"
+                                   if world > 1 else "single GPU"),
                    "l2": "per-step working set (fp16 G, 0.54 GB written and read twice) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3,
                 "pipeline": ("double-buffered inputs: the H2D copy of step i+1 overlaps step i on a copy stream"
                              + ("; forward+backward replayed as one CUDA graph (GraphedMILNCEStep)" if graphed else ""))},
-        "gpu_launches": 7 * (args.steps),
+        "gpu_launches": int(gpu_launches),
+        "gpu_launches_how": ("b200head_launch_count() over the graph capture x replays" if graphed
+                             else "b200head_launch_count() difference over warm-up + timed steps, scaled to the timed steps"),
+        "eager": {"ms_per_step": sec_eager / args.steps * 1e3, "gpu_launches": int(eager_launches)},
         "phases_ms": {"forward": fwd_ms, "backward": bwd_ms},
         "samples_per_s": B * args.steps / sec,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                      "frac": achieved / peak,
-                     "traffic": measured_traffic().get("milnce_step_dram_bytes") if (B, K, D, args.dtype) == (8192, 4, 512, "bf16") else None,
-                     "note": (f"algorithmic 6*B*BK*D FLOP per step / step time; peak = bf16 sustained, {pk['src']}; "
-                              "traffic = DRAM bytes of one step's four GEMM kernels (ncu --set full, profiles/r1_traffic.json)")},
+                     "regime": "burst" if burst else "sustained",
+                     "traffic": traffic.get("milnce_step_dram_bytes") if (B, K, D, args.dtype) == (8192, 4, 512, "bf16") else None,
+                     "note": (f"algorithmic 6*B*BK*D FLOP per step / step time; peak = cuBLAS bf16 "
+                              f"{'burst' if burst else 'sustained'} figure of {pk['src']} (timed region {sec:.3f} s, "
+                              f"power cap {'seen' if capped else 'not seen'}); traffic = DRAM bytes of one step "
+                              f"(ncu --set full, {traffic.get('_file')})")},
     }
+    if sustained is not None:
+        per_s, n_s, clk_sum = sustained
+        ach_s = flop_alg / per_s / 1e12
+        line["roofline_sustained"] = {"bound": "tensor", "achieved": ach_s, "peak": pk["bf16_sustained"],
+                                      "unit": "TFLOP/s", "frac": ach_s / pk["bf16_sustained"],
+                                      "ms_per_step": per_s * 1e3, "steps": n_s, "clocks": clk_sum}
+    if parity is not None:
+        line.update({"parity_checked": True, "parity": parity})
     if rank == 0:
-        line["clocks"] = clk.summary()
+        line["clocks"] = clocks
 
-    if world == 1 and not args.no_sdtw:
-        line["sdtw"] = bench_sdtw(dev, pk, args)
+    if not args.no_sdtw:
+        sd = bench_sdtw(dev, pk, args, world, rank, barrier, max_over_ranks)
+        if rank == 0:
+            line["sdtw"] = sd
     if rank == 0 and world == 1 and not args.no_cpu:
-        bs = min(args.cpu_sample_batch, B)
-        val, s = cpu_milnce(bs, K, D, 5, 1)
+        cores = host_threads()
+        val, s, n, w, kind = cpu_milnce(B, K, D, 2, 1, 30.0)
         line["cpu_baseline"] = {
-            "value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"B={bs} of {B}, K={K}, D={D}, fp32, torch CPU port of loss.py:10-18, 5 steps, {s * 1e3:.0f} ms/step"}
+            "value": val, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": (f"B={B}, K={K}, D={D}, fp32, "
+                       + ("reference loss.py (oracle/_ref)" if kind == "reference" else "torch port of loss.py:10-18")
+                       + f", {n} steps after {w} warm-up, {s * 1e3:.0f} ms/step")}
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     os.close(saved_stdout)
@@ -356,11 +514,12 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def bench_sdtw(dev, pk, args):
-    """BASELINE configs[2]: 256 pairs of 64x64, d=512, gamma=0.1, cosine, fwd+bwd."""
+def bench_sdtw(dev, pk, args, world, rank, barrier, max_over_ranks):
+    """BASELINE configs[2]: 256 pairs of 64x64, d=512, gamma=0.1, cosine, fwd+bwd, on EVERY rank
+    (pairs are independent units: no collective; value = pairs of all ranks / max-over-ranks time)."""
     import milnce_b200
     Bp, N, M, d = 256, 64, 64, 512
-    torch.manual_seed(1234)
+    torch.manual_seed(1234 + rank)
     sets = [(torch.randn(Bp, N, d, device=dev).requires_grad_(True),
              torch.randn(Bp, M, d, device=dev).requires_grad_(True)) for _ in range(4)]  # 268 MB > L2
     mod = milnce_b200.SoftDTW(True, gamma=0.1, dist_func="cosine")
@@ -371,9 +530,10 @@ def bench_sdtw(dev, pk, args):
         y.grad = None
         mod(x, y).sum().backward()
 
-    # The step is ~0.16 ms of GPU work behind ~8 launches: from Python it is launch-bound, so each
-    # input set's forward+backward is captured once and replayed (same module call, CUDA graph).
+    # The step is well under 0.2 ms of GPU work behind several launches: from Python it is launch-bound,
+    # so each input set's forward+backward is captured once and replayed (same module call, CUDA graph).
     graphs = []
+    per_replay = 0
     if not args.no_graph:
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -385,8 +545,10 @@ def bench_sdtw(dev, pk, args):
             x.grad = None
             y.grad = None
             g = torch.cuda.CUDAGraph()
+            n0 = launches()
             with torch.cuda.graph(g):
                 mod(x, y).sum().backward()
+            per_replay = launches() - n0
             graphs.append(g)
 
     def step():
@@ -398,21 +560,67 @@ def bench_sdtw(dev, pk, args):
             eager(*sets[k])
 
     steps = max(args.steps, 20)
-    sec = timed(step, steps, max(args.warmup, 5), lambda: None)
+    sec = max_over_ranks(timed(step, steps, max(args.warmup, 5), barrier))
     ms = sec / steps * 1e3
-    cells = 2.0 * Bp * N * M
-    alg_bytes = 3 * 2 * Bp * N * d * 4 + 2 * Bp * (N + 2) * (M + 2) * 4  # ~210 MB
+    cells = 2.0 * Bp * N * M * world
+    alg_bytes = (3 * 2 * Bp * N * d * 4 + 2 * Bp * (N + 2) * (M + 2) * 4) * world  # ~210 MB per GPU
+
+    # e2e: pinned host X, Y in; out, dX, dY back to pinned host; every step, inside the timed region
+    xh = torch.randn(Bp, N, d).pin_memory()
+    yh = torch.randn(Bp, M, d).pin_memory()
+    oh = torch.empty(Bp).pin_memory()
+    dxh = torch.empty(Bp, N, d).pin_memory()
+    dyh = torch.empty(Bp, M, d).pin_memory()
+    xd, yd = sets[0]
+    kgraph = graphs[0] if graphs else None
+    out_static = [None]
+    if kgraph is not None:
+        # a graph whose output tensor is kept, for the D2H read
+        xd.grad = None
+        yd.grad = None
+        kgraph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(kgraph):
+            out_static[0] = mod(xd, yd)
+            out_static[0].sum().backward()
+
+    def step_e2e():
+        with torch.no_grad():
+            xd.copy_(xh, non_blocking=True)
+            yd.copy_(yh, non_blocking=True)
+        if kgraph is not None:
+            kgraph.replay()
+            o = out_static[0]
+        else:
+            xd.grad = None
+            yd.grad = None
+            o = mod(xd, yd)
+            o.sum().backward()
+        oh.copy_(o.detach(), non_blocking=True)
+        dxh.copy_(xd.grad, non_blocking=True)
+        dyh.copy_(yd.grad, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    sec_e = max_over_ranks(timed(step_e2e, steps, 3, barrier))
+    h2d = 2 * Bp * N * d * 4
+    d2h = 2 * Bp * N * d * 4 + Bp * 4
+    traffic = measured_traffic()
     out = {"metric": "softdtw_fwd_bwd_dp_cells_per_s", "value": cells / (ms * 1e-3), "unit": "cells/s",
-           "ms_per_step": ms, "config": {"workload": "SoftDTW(gamma=0.1, cosine) fwd+bwd 256x(64x64)x512 fp32",
-                                         "l2": "4 rotating input sets (268 MB) exceed L2",
-                                         "launch": "CUDA graph replay of SoftDTW(...)(x, y).sum().backward()" if graphs else "eager"},
-           "roofline": {"bound": "hbm", "achieved": alg_bytes / (ms * 1e-3) / 1e9, "peak": pk["hbm"],
-                        "unit": "GB/s", "frac": alg_bytes / (ms * 1e-3) / 1e9 / pk["hbm"],
-                        "traffic": measured_traffic().get("sdtw_step_dram_bytes")}}
-    if not args.no_cpu:
-        val, s = cpu_sdtw(16, N, M, d)
-        out["cpu_baseline"] = {"value": val, "unit": "cells/s", "cores": 1, "kind": "port",
-                               "sample": f"16 of 256 pairs, oracle (numpy dist + C DP), {s:.2f} s"}
+           "ms_per_step": ms, "n_gpus": world, "scaling": "weak",
+           "config": {"workload": "SoftDTW(gamma=0.1, cosine) fwd+bwd 256x(64x64)x512 fp32 per GPU (BASELINE configs[2])",
+                      "l2": "4 rotating input sets (268 MB) exceed L2",
+                      "launch": "CUDA graph replay of SoftDTW(...)(x, y).sum().backward()" if graphs else "eager",
+                      "parallelism": f"{world} x 256 independent pairs, no collective" if world > 1 else "single GPU"},
+           "gpu_launches": int(per_replay * steps) if graphs else None,
+           "e2e": {"value": cells / (sec_e / steps), "unit": "cells/s", "ms_per_step": sec_e / steps * 1e3,
+                   "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                   "pipeline": "pinned host X, Y -> device, fwd+bwd, out and dX, dY -> pinned host; not overlapped"},
+           "roofline": {"bound": "hbm", "achieved": alg_bytes / (ms * 1e-3) / 1e9, "peak": pk["hbm"] * world,
+                        "unit": "GB/s", "frac": alg_bytes / (ms * 1e-3) / 1e9 / (pk["hbm"] * world),
+                        "traffic": traffic.get("sdtw_step_dram_bytes")}}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        val, s, kind, note = cpu_sdtw(Bp, N, M, d)
+        out["cpu_baseline"] = {"value": val, "unit": "cells/s", "cores": host_threads(), "kind": kind,
+                               "sample": f"all {Bp} pairs once, {note}, {s:.2f} s (the recurrences are single-threaded)"}
     return out
 
 

@@ -82,7 +82,9 @@ class CudaBackend:
 
     @staticmethod
     def forward_shard(video, text, i0, n):
-        """Returns (row_lse[B] (own entries valid), col_part[B], nom[B] (own entries valid), ws)."""
+        """Returns (pack, ws): pack = [row_lse of the n owned samples | their nom | col_part of all B
+        samples], float32, 2n + B entries - the buffer the ranks all-gather (the kernels write it
+        in place: no torch.cat in the step)."""
         lib = _lib.load()
         B, D = video.shape
         K = text.shape[0] // B
@@ -90,14 +92,17 @@ class CudaBackend:
         dev = video.device
         nbytes = lib.milnce_workspace_bytes(B, K, D, code, n)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        row = torch.empty(B, dtype=torch.float32, device=dev)
-        colp = torch.empty(B, dtype=torch.float32, device=dev)
-        nom = torch.empty(B, dtype=torch.float32, device=dev)
+        pack = torch.empty(2 * n + B, dtype=torch.float32, device=dev)
+        # the C ABI writes entries [i0, i0+n) of row_lse and nom: hand it bases such that those
+        # entries are pack[0:n] and pack[n:2n]
+        row_base = ctypes.c_void_p(pack.data_ptr() - 4 * i0)
+        nom_base = ctypes.c_void_p(pack.data_ptr() + 4 * n - 4 * i0)
+        col_base = ctypes.c_void_p(pack.data_ptr() + 8 * n)
         with torch.cuda.device(dev):
-            rc = lib.milnce_forward_shard(_ptr(video), _ptr(text), B, K, D, code, i0, n, _ptr(row),
-                                          _ptr(colp), _ptr(nom), _ptr(ws), nbytes, _lib.stream_ptr(dev))
+            rc = lib.milnce_forward_shard(_ptr(video), _ptr(text), B, K, D, code, i0, n, row_base,
+                                          col_base, nom_base, _ptr(ws), nbytes, _lib.stream_ptr(dev))
         _lib.check(rc, "milnce_forward_shard")
-        return row, colp, nom, ws
+        return pack, ws
 
     @staticmethod
     def shard_combine(gathered, world, b):

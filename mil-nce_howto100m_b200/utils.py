@@ -51,90 +51,135 @@ class AllGather(torch.autograd.Function):
         )
 
 
+# ---------------------------------------------------------------------------------------------
+# the fused gather -> loss -> local-slice module
+# ---------------------------------------------------------------------------------------------
+def _gather_embeddings(v, t, world, group):
+    """All-gather of the video AND text shards as ONE collective call (reference utils.py:13-17 x 2:
+    two list all_gathers and two cats).  NCCL runs the pair as a single grouped kernel; a backend
+    without coalescing support (gloo on CPU) gets two plain calls."""
+    V = torch.empty((world * v.shape[0], v.shape[1]), dtype=v.dtype, device=v.device)
+    T = torch.empty((world * t.shape[0], t.shape[1]), dtype=t.dtype, device=t.device)
+    pg = group if group is not None else dist.group.WORLD
+    if dist.get_backend(pg) == "nccl":
+        with dist._coalescing_manager(group=pg, device=v.device, async_ops=True) as cm:
+            dist.all_gather_into_tensor(V, v, group=pg)
+            dist.all_gather_into_tensor(T, t, group=pg)
+        cm.wait()
+        return V, T
+    h1 = dist.all_gather_into_tensor(V, v, group=group, async_op=True)
+    h2 = dist.all_gather_into_tensor(T, t, group=group, async_op=True)
+    h1.wait()
+    h2.wait()
+    return V, T
+
+
+def _mark(marks, name, dev):
+    """Phase stamp for the timeline tool (profiles/multi_timeline.py); a no-op in normal use."""
+    if marks is not None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(dev))
+        marks.append((name, ev))
+
+
 class _GatheredMILNCE(torch.autograd.Function):
+    """Row block + column block per rank ("rowcol"): 6/W GEMM units, no gradient collective."""
+
     @staticmethod
-    def forward(ctx, video_local, text_local, world, rank, group, backend):
+    def forward(ctx, video_local, text_local, world, rank, group, backend, opts):
         b = video_local.shape[0]
         v = video_local.detach().contiguous()
         t = text_local.detach().contiguous()
+        marks = opts.get("marks")
+        _mark(marks, "start", v.device)
         if world > 1:
-            V = torch.empty((world * b, v.shape[1]), dtype=v.dtype, device=v.device)
-            T = torch.empty((world * t.shape[0], t.shape[1]), dtype=t.dtype, device=t.device)
-            h1 = dist.all_gather_into_tensor(V, v, group=group, async_op=True)
-            h2 = dist.all_gather_into_tensor(T, t, group=group, async_op=True)
-            h1.wait()
-            h2.wait()
+            V, T = _gather_embeddings(v, t, world, group)
         else:
             V, T = v, t
+        _mark(marks, "gather_embeddings", v.device)
         i0 = rank * b
         loss_part, den, nom, ws = backend.forward(V, T, i0, b)
+        _mark(marks, "forward_kernels", v.device)
         if world > 1:
-            # 4*B bytes: every rank needs den of every sample for its column block
-            den_all = torch.empty_like(den)
-            dist.all_gather_into_tensor(den_all, den[i0:i0 + b].contiguous(), group=group)
-            dist.all_reduce(loss_part, op=dist.ReduceOp.SUM, group=group)
-            den = den_all
+            # one small all-gather: [den of my samples | my share of the loss]; every rank needs den
+            # of every sample for its column block, and the loss is the sum of the shares
+            pack = torch.cat([den[i0:i0 + b], loss_part.reshape(1).to(den.dtype)])
+            allp = torch.empty(world * (b + 1), dtype=pack.dtype, device=pack.device)
+            dist.all_gather_into_tensor(allp, pack, group=group)
+            allp = allp.view(world, b + 1)
+            den = allp[:, :b].reshape(world * b).contiguous()
+            loss = allp[:, b].sum()
+        else:
+            loss = loss_part[0]
+        _mark(marks, "stats_exchange", v.device)
         ctx.save_for_backward(V, T, den, nom)
         ctx.ws = ws
-        ctx.meta = (i0, b, backend, v.dtype, t.dtype)
-        return loss_part[0]
-
-    @staticmethod
-    def backward(ctx, grad_output):
-        V, T, den, nom = ctx.saved_tensors
-        i0, b, backend, vdt, tdt = ctx.meta
-        g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
-        dv, dt = backend.backward(V, T, den, nom, g, i0, b, ctx.ws)
-        ctx.ws = None
-        # exactly the slice AllGather.backward returns: no gradient collective (utils.py:20-24)
-        return dv.to(vdt), dt.to(tdt), None, None, None, None
-
-
-class _GatheredMILNCERows(torch.autograd.Function):
-    """Rows-only sharding: each rank computes only its rows of the similarity matrix.
-
-    Exchanges: all-gather of the embeddings (as in the reference), one all-gather of
-    2*b + B floats per rank (row statistic, positives, partial column statistic) and one
-    reduce-scatter of the (B*K, D) float32 partial text gradient in backward.  Per-rank GEMM
-    work is 4/W of the single-GPU step (6/W for the row+column block scheme above)."""
-
-    @staticmethod
-    def forward(ctx, video_local, text_local, world, rank, group, backend):
-        b = video_local.shape[0]
-        v = video_local.detach().contiguous()
-        t = text_local.detach().contiguous()
-        V = torch.empty((world * b, v.shape[1]), dtype=v.dtype, device=v.device)
-        T = torch.empty((world * t.shape[0], t.shape[1]), dtype=t.dtype, device=t.device)
-        h1 = dist.all_gather_into_tensor(V, v, group=group, async_op=True)
-        h2 = dist.all_gather_into_tensor(T, t, group=group, async_op=True)
-        h1.wait()
-        h2.wait()
-        B = world * b
-        i0 = rank * b
-        row, colp, nom, ws = backend.forward_shard(V, T, i0, b)
-        # one small all-gather: [row_lse of my samples | nom of my samples | my column partials]
-        pack = torch.cat([row[i0:i0 + b], nom[i0:i0 + b], colp]).contiguous()
-        allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
-        dist.all_gather_into_tensor(allp, pack, group=group)
-        den, nom_all, loss = backend.shard_combine(allp.view(world, 2 * b + B), world, b)
-        ctx.save_for_backward(V, T, den, nom_all)
-        ctx.ws = ws
-        ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0])
+        ctx.meta = (i0, b, backend, v.dtype, t.dtype, marks)
         return loss
 
     @staticmethod
     def backward(ctx, grad_output):
         V, T, den, nom = ctx.saved_tensors
-        i0, b, backend, vdt, tdt, group, bk_local = ctx.meta
+        i0, b, backend, vdt, tdt, marks = ctx.meta
+        _mark(marks, "backward_start", V.device)
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
+        dv, dt = backend.backward(V, T, den, nom, g, i0, b, ctx.ws)
+        ctx.ws = None
+        _mark(marks, "backward_kernels", V.device)
+        # exactly the slice AllGather.backward returns: no gradient collective (utils.py:20-24)
+        return dv.to(vdt), dt.to(tdt), None, None, None, None, None
+
+
+class _GatheredMILNCERows(torch.autograd.Function):
+    """Rows-only sharding: each rank computes only its rows of the similarity matrix.
+
+    Exchanges: one grouped all-gather of the embeddings (as in the reference), one all-gather of
+    2*b + B floats per rank (row statistic, positives, partial column statistic) and one
+    reduce-scatter of the (B*K, D) partial text gradient in backward (bfloat16 or float32 on the
+    wire).  Per-rank GEMM work is 4/W of the single-GPU step (6/W for the row+column block scheme)."""
+
+    @staticmethod
+    def forward(ctx, video_local, text_local, world, rank, group, backend, opts):
+        b = video_local.shape[0]
+        v = video_local.detach().contiguous()
+        t = text_local.detach().contiguous()
+        marks = opts.get("marks")
+        _mark(marks, "start", v.device)
+        V, T = _gather_embeddings(v, t, world, group)
+        _mark(marks, "gather_embeddings", v.device)
+        B = world * b
+        i0 = rank * b
+        # the kernels write [row_lse of my samples | nom of my samples | my column partials] in place
+        pack, ws = backend.forward_shard(V, T, i0, b)
+        _mark(marks, "forward_kernels", v.device)
+        allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
+        dist.all_gather_into_tensor(allp, pack, group=group)
+        _mark(marks, "stats_exchange", v.device)
+        den, nom_all, loss = backend.shard_combine(allp.view(world, 2 * b + B), world, b)
+        _mark(marks, "combine", v.device)
+        ctx.save_for_backward(V, T, den, nom_all)
+        ctx.ws = ws
+        ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0], marks, opts.get("partial_dtype"))
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        V, T, den, nom = ctx.saved_tensors
+        i0, b, backend, vdt, tdt, group, bk_local, marks, pdt = ctx.meta
+        _mark(marks, "backward_start", V.device)
+        g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
+        pdt = pdt if pdt is not None else torch.float32
         # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
-        _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1)
+        _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt)
+        _mark(marks, "gradient_tiles+dtext_partial", V.device)
         dt = torch.empty((bk_local, dt_partial.shape[1]), dtype=dt_partial.dtype, device=dt_partial.device)
         work = dist.reduce_scatter_tensor(dt, dt_partial, op=dist.ReduceOp.SUM, group=group, async_op=True)
         dv, _ = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=2, grad_dtype=vdt)
         ctx.ws = None
+        _mark(marks, "dvideo", V.device)
         work.wait()
-        return dv, dt.to(tdt), None, None, None, None
+        _mark(marks, "reduce_scatter_done", V.device)
+        return dv, dt.to(tdt), None, None, None, None, None
 
 
 class GatheredMILNCELoss(torch.nn.Module):
@@ -146,17 +191,23 @@ class GatheredMILNCELoss(torch.nn.Module):
     embeddings of this rank.
     """
 
-    def __init__(self, args=None, group=None, backend=None, scheme="auto"):
+    def __init__(self, args=None, group=None, scheme="auto", partial_dtype=None, _backend=None):
         """scheme: "rows" (each rank computes only its rows of S, reduce-scatter of the text
         gradient; bf16 embeddings), "rowcol" (row block + column block per rank, no gradient
-        collective - the reference's communication pattern), or "auto" (rows when available)."""
+        collective - the reference's communication pattern), or "auto" (rows when available).
+        partial_dtype: dtype of the rows scheme's text-gradient partials on the wire (default:
+        float32; torch.bfloat16 halves the reduce-scatter).
+        _backend: private test seam (the CPU tests drive the orchestration with a stand-in)."""
         super().__init__()
         if scheme not in ("auto", "rows", "rowcol"):
             raise ValueError("scheme must be 'auto', 'rows' or 'rowcol'")
         self.args = args
         self.group = group
-        self._backend = backend
+        self._backend = _backend
         self.scheme = scheme
+        self.partial_dtype = partial_dtype
+        self.last_scheme = None
+        self._marks = None   # set to a list by profiles/multi_timeline.py to collect phase stamps
 
     def forward(self, video_embd, text_embd):
         from .loss import CudaBackend, _validate
@@ -172,5 +223,7 @@ class GatheredMILNCELoss(torch.nn.Module):
                 raise RuntimeError("scheme='rows' needs bfloat16 embeddings and a local batch that is a "
                                    "multiple of 8")
             use_rows = ok
+        self.last_scheme = "rows" if use_rows else ("rowcol" if world > 1 else "single")
         fn = _GatheredMILNCERows if use_rows else _GatheredMILNCE
-        return fn.apply(video_embd, text_embd, world, rank, self.group, backend)
+        opts = {"marks": self._marks, "partial_dtype": self.partial_dtype}
+        return fn.apply(video_embd, text_embd, world, rank, self.group, backend, opts)

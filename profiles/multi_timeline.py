@@ -1,0 +1,143 @@
+"""Per-phase timeline of one GatheredMILNCELoss step on W GPUs (CUDA events, max over ranks).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node W --master-addr 127.0.0.1 \
+        --master-port 29511 profiles/multi_timeline.py [--out profiles/r2_multi_timeline_W.txt]
+
+For every scheme ("rows" with float32 and with bfloat16 text-gradient partials, "rowcol") the step is
+run with phase stamps (the module's _marks hook: one CUDA event on the compute stream after each
+phase; a collective's stamp is recorded after its wait(), i.e. when the compute stream may go on).
+Also timed alone: the collectives of the step at their real sizes.  B=8192, K=4, D=512, bf16.
+"""
+import argparse
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--batch", type=int, default=8192)
+    args = ap.parse_args()
+    import milnce_b200
+    world = int(os.environ["WORLD_SIZE"])
+    rank = int(os.environ["RANK"])
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    B, K, D = args.batch, 4, 512
+    b = B // world
+    g = torch.Generator().manual_seed(1000 + rank)
+    v = (torch.randn(b, D, generator=g) * 0.05).bfloat16().to(dev).requires_grad_(True)
+    t = (torch.randn(b * K, D, generator=g) * 0.05).bfloat16().to(dev).requires_grad_(True)
+    lines = [f"# GatheredMILNCELoss step timeline, W={world}, B={B} K={K} D={D} bf16; microseconds, median over "
+             f"{args.steps} steps, max over ranks"]
+
+    def allmax(x):
+        tt = torch.tensor(x, dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return tt.tolist()
+
+    variants = [("rows/f32-partial", dict(scheme="rows", partial_dtype=torch.float32)),
+                ("rows/bf16-partial", dict(scheme="rows", partial_dtype=torch.bfloat16)),
+                ("rowcol", dict(scheme="rowcol"))]
+    for name, kw in variants:
+        mod = milnce_b200.GatheredMILNCELoss(**kw)
+        for _ in range(5):
+            v.grad = t.grad = None
+            mod(v, t).backward()
+        # whole step, no stamps
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            v.grad = t.grad = None
+            mod(v, t).backward()
+        e1.record()
+        torch.cuda.synchronize()
+        whole = allmax([e0.elapsed_time(e1) / args.steps * 1e3])[0]
+        # stamped steps
+        per_phase = {}
+        order = []
+        for _ in range(args.steps):
+            mod._marks = []
+            v.grad = t.grad = None
+            dist.barrier()
+            mod(v, t).backward()
+            torch.cuda.synchronize()
+            mk = mod._marks
+            for (n0, a), (n1, c) in zip(mk[:-1], mk[1:]):
+                key = n1
+                if key not in per_phase:
+                    per_phase[key] = []
+                    order.append(key)
+                per_phase[key].append(a.elapsed_time(c) * 1e3)
+        mod._marks = None
+        med = [sorted(per_phase[k])[len(per_phase[k]) // 2] for k in order]
+        med = allmax(med)
+        lines.append(f"\n## {name}: whole step {whole:.0f} us (back to back, no stamps)")
+        for k, m in zip(order, med):
+            note = "   (autograd glue between forward and backward; host-side)" if k == "backward_start" else ""
+            lines.append(f"  {k:34s} {m:8.0f}{note}")
+        lines.append(f"  {'sum of phases':34s} {sum(med):8.0f}")
+
+    # the collectives alone
+    lines.append("\n## collectives alone (CUDA events around 20 back-to-back calls)")
+
+    def time_coll(fn, n=20):
+        for _ in range(3):
+            fn()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return allmax([e0.elapsed_time(e1) / n * 1e3])[0]
+
+    Vb = torch.empty(B, D, dtype=torch.bfloat16, device=dev)
+    Tb = torch.empty(B * K, D, dtype=torch.bfloat16, device=dev)
+    vd, td = v.detach(), t.detach()
+
+    def gather2():
+        with dist._coalescing_manager(device=dev, async_ops=True) as cm:
+            dist.all_gather_into_tensor(Vb, vd)
+            dist.all_gather_into_tensor(Tb, td)
+        cm.wait()
+
+    def gather_sep():
+        dist.all_gather_into_tensor(Vb, vd)
+        dist.all_gather_into_tensor(Tb, td)
+
+    small = torch.empty(2 * b + B, device=dev)
+    small_all = torch.empty(world * (2 * b + B), device=dev)
+    p32 = torch.empty(B * K, D, device=dev)
+    o32 = torch.empty(b * K, D, device=dev)
+    p16 = torch.empty(B * K, D, dtype=torch.bfloat16, device=dev)
+    o16 = torch.empty(b * K, D, dtype=torch.bfloat16, device=dev)
+    lines.append(f"  all-gather video+text, one grouped call ({(Vb.numel() + Tb.numel()) * 2 / 1e6:.0f} MB out)  {time_coll(gather2):8.0f}")
+    lines.append(f"  all-gather video, text as two calls                          {time_coll(gather_sep):8.0f}")
+    lines.append(f"  all-gather of the statistics ({small.numel() * 4 / 1e3:.0f} KB per rank)                {time_coll(lambda: dist.all_gather_into_tensor(small_all, small)):8.0f}")
+    lines.append(f"  reduce-scatter dtext partial float32 ({p32.numel() * 4 / 1e6:.0f} MB in)              {time_coll(lambda: dist.reduce_scatter_tensor(o32, p32)):8.0f}")
+    lines.append(f"  reduce-scatter dtext partial bfloat16 ({p16.numel() * 2 / 1e6:.0f} MB in)             {time_coll(lambda: dist.reduce_scatter_tensor(o16, p16)):8.0f}")
+    if rank == 0:
+        text = "\n".join(lines) + "\n"
+        print(text)
+        if args.out:
+            with open(args.out, "w") as f:
+                f.write(text)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

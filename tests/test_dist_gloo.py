@@ -6,7 +6,7 @@ the orchestration that bench.py --gpus N and the train-step call site rely on:
 * ``AllGather`` reproduces reference utils.py:11-24 (rank-ordered concat forward,
   local slice backward with no reduction);
 * ``GatheredMILNCELoss`` shards the loss over ranks (row block + column block per
-  rank, one den all-gather, one scalar all-reduce) and still returns the global
+  rank, one all-gather of den and the loss shares) and still returns the global
   loss and exactly the local gradient slices of the gathered reference loss.
 """
 import os
@@ -80,7 +80,7 @@ class OracleBackend:
         nm[i0:i0 + n] = nom[i0:i0 + n]
         # partial column statistic over the OWNED rows only, for every sample j
         colp = milnce_oracle._lse(np.transpose(x[i0:i0 + n], (1, 0, 2)).reshape(B, n * K), axis=1)
-        return torch.from_numpy(row), torch.from_numpy(colp), torch.from_numpy(nm), None
+        return torch.from_numpy(np.concatenate([row[i0:i0 + n], nm[i0:i0 + n], colp])), None
 
     @staticmethod
     def shard_combine(allp, world, b):
@@ -92,7 +92,7 @@ class OracleBackend:
         return den, nom_all, (den - nom_all).mean()
 
     @staticmethod
-    def backward_shard(V, T, den, nom, g, i0, n, ws, parts=3, grad_dtype=None):
+    def backward_shard(V, T, den, nom, g, i0, n, ws, parts=3, grad_dtype=None, partial_dtype=None):
         v = V.double().numpy()
         t = T.double().numpy()
         B = v.shape[0]
@@ -147,7 +147,7 @@ def _worker(rank, world, port, b, K, D, scheme, out):
         v_loc.grad = None
 
         # 2. sharded loss == reference loss on gathered tensors, grads == local slices
-        mod = milnce_b200.GatheredMILNCELoss(args=args, backend=OracleBackend, scheme=scheme)
+        mod = milnce_b200.GatheredMILNCELoss(args=args, _backend=OracleBackend, scheme=scheme)
         loss = mod(v_loc, t_loc)
         (loss * 1.75).backward()  # 1.75 is exact in float32 (grad_loss is passed as fp32)
         ref_loss, ref_dv, ref_dt, _, _ = milnce_oracle.milnce_closed_form(V.numpy(), T.numpy(), 1.75)
@@ -176,7 +176,7 @@ def test_world_size_one_needs_no_process_group():
     g = torch.Generator().manual_seed(5)
     V = (torch.randn(6, 8, generator=g, dtype=torch.float64)).requires_grad_(True)
     T = (torch.randn(12, 8, generator=g, dtype=torch.float64)).requires_grad_(True)
-    loss = milnce_b200.GatheredMILNCELoss(backend=OracleBackend)(V, T)
+    loss = milnce_b200.GatheredMILNCELoss(_backend=OracleBackend)(V, T)
     loss.backward()
     ref_loss, ref_dv, ref_dt, _, _ = milnce_oracle.milnce_closed_form(V.detach().numpy(),
                                                                      T.detach().numpy())

@@ -181,16 +181,15 @@ def test_rows_only_sharding_emulated_on_one_gpu():
     t = (torch.randn(B * K, D, generator=g) * 0.2).bfloat16().cuda()
     loss, dv, dt, den, nom = _raw(v, t)
     b = B // W
-    outs = [CudaBackend.forward_shard(v, t, r * b, b) for r in range(W)]
-    row_all = torch.cat([o[0][r * b:(r + 1) * b] for r, o in enumerate(outs)])
-    nom_all = torch.cat([o[2][r * b:(r + 1) * b] for r, o in enumerate(outs)])
-    col_all = torch.logsumexp(torch.stack([o[1] for o in outs]), dim=0)
+    outs = [CudaBackend.forward_shard(v, t, r * b, b) for r in range(W)]   # (pack, ws) per rank
+    row_all = torch.cat([o[0][:b] for o in outs])
+    nom_all = torch.cat([o[0][b:2 * b] for o in outs])
+    col_all = torch.logsumexp(torch.stack([o[0][2 * b:] for o in outs]), dim=0)
     den_all = torch.logaddexp(row_all, col_all)
     assert torch.allclose(den_all, den, rtol=2e-6, atol=0)
     assert torch.allclose(nom_all, nom, rtol=1e-6, atol=0)
     # the fused combine kernel on the gathered layout (W, 2b + B)
-    gathered = torch.stack([torch.cat([o[0][r * b:(r + 1) * b], o[2][r * b:(r + 1) * b], o[1]])
-                            for r, o in enumerate(outs)]).contiguous()
+    gathered = torch.stack([o[0] for o in outs]).contiguous()
     den_c, nom_c, loss_c = CudaBackend.shard_combine(gathered, W, b)
     assert torch.allclose(den_c, den, rtol=2e-6, atol=0)
     assert torch.equal(nom_c, nom_all)
@@ -199,13 +198,13 @@ def test_rows_only_sharding_emulated_on_one_gpu():
     dt_sum = torch.zeros_like(dt)
     for r, o in enumerate(outs):
         if r % 2 == 0:
-            dvr, dtp = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[3])
+            dvr, dtp = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[1])
         else:
             # split form (what GatheredMILNCELoss uses to overlap the reduce-scatter): the text partial
             # first, then dvideo from the gradient tiles left in the workspace, here written as bf16
-            none, dtp = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[3], parts=1)
+            none, dtp = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[1], parts=1)
             assert none is None
-            dvr, none = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[3], parts=2,
+            dvr, none = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[1], parts=2,
                                                    grad_dtype=torch.bfloat16)
             assert none is None and dvr.dtype == torch.bfloat16
         tol = 5e-6 if dvr.dtype == torch.float32 else 3e-3  # bf16 output: 2^-9 rounding per element
