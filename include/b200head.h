@@ -187,8 +187,8 @@ int b200head_gemm_at_f16(const void *At, const void *Bm, float *C, int M, int N,
                          int ldat, int ldb, int ldc, float alpha, void *stream);
 /* Same products through the CTA-pair kernel (tcgen05.mma.cta_group::2, 256 x 256 tiles) that
  * the bf16 path uses; a_transposed bit 0: A is passed as (Kd, M) like b200head_gemm_at_f16, bit 1: Bm is
- * passed as (Kd, N) (MN-major B operand, how the gradient GEMMs read text and video); bit 2: A holds
- * bfloat16 instead of float16; bit 3: Bm holds bfloat16 (the two operand formats are independent). */
+ * passed as (Kd, N) (MN-major B operand, how the gradient GEMMs read text and video); bit 2: both
+ * operands hold bfloat16 instead of float16. */
 int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M, int N, int Kd,
                        int lda, int ldb, int ldc, float alpha, int a_transposed, void *stream);
 

@@ -322,8 +322,6 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // bf16 fast path, first pass over the inputs (one launch instead of three): one warp per sample i
-// (absmax_bits == nullptr: the operands go to the tensor cores as they are, only the positives are wanted;
-// the grid then covers the n owned samples, B and i0 are passed as i0 + n and i0)
 // reads video[i] and its K candidates text[iK .. iK+K) once and produces
 //   - the running |x|max of both tensors (atomicMax on the float bits, like absmax_kernel)
 //   - nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs on the original values
@@ -354,9 +352,8 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
             f[2 * j + 1] = v.y;
         }
     };
-    for (int i = (absmax_bits == nullptr ? i0 : 0) + blockIdx.x * wpb + (threadIdx.x >> 5); i < B; i += gridDim.x * wpb) {
+    for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < B; i += gridDim.x * wpb) {
         const bool want_nom = (nom != nullptr) && i >= i0 && i < i0 + n;
-        if (absmax_bits == nullptr && !want_nom) continue;  // positives only: nothing to do for this sample
         const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
         float pm = -INFINITY, ps = 0.f;
 #pragma unroll 2
@@ -385,7 +382,6 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
         }
         if (want_nom && lane == 0) nom[i] = pm + logf(ps);
     }
-    if (absmax_bits == nullptr) return;  // (kernel-uniform)
     mv = warp_max(mv);
     mt = warp_max(mt);
     __shared__ float sv[8], stx[8];
@@ -695,32 +691,20 @@ int launch_epig2(Args... a) {
     else return launch_gemm2<tc::EpiG, false, false, false>(a...);
 }
 
-// bfloat16 inputs with 16-byte aligned rows go to the tensor cores AS THEY ARE: tcgen05.mma.kind::f16 takes
-// the format of A and of B separately, so S = V . T^T runs bf16 x bf16 and the gradient GEMMs multiply
-// the fp16 gradient tiles by the bf16 embeddings.  No staged fp16 copy, no |x|max pass, no scale.
-// (-DB200_DIRECT_BF16=0 in a variant build forces the staged path for A/B timing.)
-#ifndef B200_DIRECT_BF16
-#define B200_DIRECT_BF16 1
-#endif
-bool direct_bf16(const Plan &p, const void *video, const void *text) {
-    return B200_DIRECT_BF16 != 0 && p.dtype == B200HEAD_BF16 && p.D % 8 == 0 &&
-           ((((uintptr_t)video) | ((uintptr_t)text)) & 15) == 0;
-}
-// What the GEMMs read: the staged fp16 operands in the workspace, or the caller's bf16 tensors.
+// What the GEMMs read: the staged fp16 operands in the workspace and the scalars that un-scale them.
+// (Feeding the caller's bf16 tensors to the tensor cores directly is not an option for the gradient
+// GEMMs: tcgen05.mma.kind::f16 with A = fp16 gradient tiles and B = bf16 embeddings - two different
+// operand formats in one instruction - raises an illegal-instruction fault on sm_100a, and bf16
+// gradient tiles cost 1.7e-3 of accuracy.)
 struct Operands {
-    const __half *vk, *tk;      // K-major video (B, ld_vk) and text (BK, ld_tk) (bf16 bits when direct)
+    const __half *vk, *tk;      // K-major video (B, ld_vk) and text (BK, ld_tk)
     long long ld_vk, ld_tk;
-    const float *inv_ss, *s_video, *s_text;  // device scalars; null when direct (scale 1)
-    uint32_t fmt_s;             // S = V . T^T:  both operands
-    uint32_t fmt_b;             // gradient GEMMs: the B operand (text or video); A is the fp16 G
+    const float *inv_ss, *s_video, *s_text;  // device scalars
 };
-Operands operands(const Plan &p, const void *video, const void *text, uint8_t *ws) {
+Operands operands(const Plan &p, uint8_t *ws) {
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    if (direct_bf16(p, video, text))
-        return Operands{(const __half *)video, (const __half *)text, (long long)p.D, (long long)p.D, nullptr, nullptr,
-                        nullptr, tc::IDESC_A_BF16 | tc::IDESC_B_BF16, tc::IDESC_B_BF16};
     return Operands{reinterpret_cast<const __half *>(ws + p.off_vk), reinterpret_cast<const __half *>(ws + p.off_tk),
-                    p.ld_vk, p.ld_tk, &sc->inv_ss, &sc->s_video, &sc->s_text, 0u, 0u};
+                    p.ld_vk, p.ld_tk, &sc->inv_ss, &sc->s_video, &sc->s_text};
 }
 
 // Stages video/text into the fp16 operands.  When `nom` is non-null the positives' log-sum-exp of
@@ -734,16 +718,6 @@ int stage_inputs(const Plan &p, const T *video, const T *text, uint8_t *ws, cuda
     bool fast = false;
     if constexpr (std::is_same<T, __nv_bfloat16>::value) {
         fast = (p.D % 8 == 0) && (((uintptr_t)video & 15) == 0) && (((uintptr_t)text & 15) == 0);
-        if (direct_bf16(p, video, text)) {
-            // nothing to stage; only the positives of the owned samples (one warp each)
-            if (nom != nullptr) {
-                const int wpb = 8;
-                B200_CUDA_OK(b200::launch_pdl(prep_bf16_kernel, dim3((p.n + wpb - 1) / wpb), dim3(wpb * 32), 0, st,
-                                              video, text, p.i0 + p.n, p.K, p.D, p.i0, p.n, nom,
-                                              (unsigned int *)nullptr));
-            }
-            return 0;
-        }
         if (fast) {
             const int wpb = 8;
             const int blocks = std::min((p.B + wpb - 1) / wpb, 8 * num_sms());
@@ -802,9 +776,9 @@ int check_common(const Plan &p, const void *ws, size_t ws_bytes) {
 template <int G>
 int launch_stats2_g(const float *scale, float *pr, long long ldr, float *pc, long long ldc, const void *A,
                     long long lda, const void *Bm, long long ldb, int M, int N, int Kd, cudaStream_t st,
-                    const char *what, uint32_t fmt) {
+                    const char *what) {
     typename tc::EpiRowColT<G>::Params e{pr, ldr, pc, ldc, scale};
-    return launch_gemm2<tc::EpiRowColT<G>>(A, lda, Bm, ldb, M, N, Kd, e, st, what, fmt);
+    return launch_gemm2<tc::EpiRowColT<G>>(A, lda, Bm, ldb, M, N, Kd, e, st, what);
 }
 template <class... Args>
 int launch_stats2(int cg, Args... a) {
@@ -822,7 +796,7 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
     int rc = stage_inputs<T>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    const Operands o = operands(p, video, text, ws);
+    const Operands o = operands(p, ws);
     const __half *vk = o.vk, *tk = o.tk;
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
@@ -834,7 +808,7 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         const char *what = "milnce forward (fused row+column statistics)";
         if (p.P == 1) {
             rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, ldc, vk, o.ld_vk, tk, o.ld_tk, p.B,
-                               (int)p.BK, Kd, st, what, o.fmt_s);
+                               (int)p.BK, Kd, st, what);
         } else {
             tc::EpiRowCol::Params e{pr, (long long)p.n, pc, ldc, o.inv_ss};
             rc = launch_gemm<tc::EpiRowCol>(vk, o.ld_vk, tk, o.ld_tk, p.B, (int)p.BK, Kd, p.chunk_s, e, st, what);
@@ -847,10 +821,10 @@ int forward_impl(const Plan &p, const T *video, const T *text, float *den, float
         const __half *tb = tk + (size_t)p.i0 * p.K * o.ld_tk;
         if (p.P == 1) {
             rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, nullptr, 0, va, o.ld_vk, tk, o.ld_tk, p.n,
-                               (int)p.BK, Kd, st, "milnce forward row block", o.fmt_s);
+                               (int)p.BK, Kd, st, "milnce forward row block");
             if (rc) return rc;
             rc = launch_stats2(p.cg, o.inv_ss, nullptr, 0, pc, ldc, vk, o.ld_vk, tb, o.ld_tk, p.B,
-                               p.n * p.K, Kd, st, "milnce forward column block", o.fmt_s);
+                               p.n * p.K, Kd, st, "milnce forward column block");
         } else {
             tc::EpiRowCol::Params er{pr, (long long)p.n, nullptr, 0, o.inv_ss};
             rc = launch_gemm<tc::EpiRowCol>(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, er, st,
@@ -889,7 +863,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     if (!(reuse && p.n == p.B))
         B200_CUDA_OK(b200::launch_pdl(scalars_backward_kernel, dim3(1), dim3(1024), 0, st, sc, grad_loss, den, p.B));
     const float alpha0 = 1.f / ((float)p.B * tc::G_SCALE);
-    const Operands o = operands(p, video, text, ws);
+    const Operands o = operands(p, ws);
     const __half *vk = o.vk, *tk = o.tk;
     const __half *vt = reinterpret_cast<const __half *>(ws + p.off_vt);
     const __half *tt = reinterpret_cast<const __half *>(ws + p.off_tt);
@@ -901,7 +875,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, p.P, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), o.inv_ss, fast};
     const __half *va = vk + (size_t)p.i0 * o.ld_vk;
     rc = (p.P == 1) ? launch_epig2(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, gr, st,
-                                           "milnce backward row block", o.fmt_s)
+                                           "milnce backward row block")
                     : launch_gemm<tc::EpiG>(va, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, Kd, p.chunk_s, gr, st,
                                             "milnce backward row block");
     if (rc) return rc;
@@ -910,7 +884,7 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
     // n-fastest tile order: the CTAs in flight share G rows through L2 (G was re-read from HBM once
     // per 128-column block of D before: 2.2 GB instead of 0.54 GB for the dtext GEMM).
     rc = (p.P == 1) ? launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                            "milnce dvideo GEMM", o.fmt_b)
+                                            "milnce dvideo GEMM")
                     : launch_gemm<tc::EpiStore, false, 1, true>(g, p.ld_g, tt, p.ld_tt, p.n, p.D,
                                                                 (int)(p.P * p.BK), p.chunk_g, sv, st,
                                                                 "milnce dvideo GEMM");
@@ -926,13 +900,13 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
             tc::EpiG::Params gc{den, nom, gt, p.ld_g2, (long long)p.n * p.K, 1, 0, tc::make_fastdiv(1), p.i0 * p.K, tc::make_fastdiv(p.K),
                                 o.inv_ss, fast};
             rc = launch_epig2(vk, o.ld_vk, tk + (size_t)p.i0 * p.K * o.ld_tk, o.ld_tk, p.B,
-                                        p.n * p.K, Kd, gc, st, "milnce backward column block", o.fmt_s);
+                                        p.n * p.K, Kd, gc, st, "milnce backward column block");
             if (rc) return rc;
             g2 = gt;
             ld_g2 = p.ld_g2;
         }
         rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g2, ld_g2, vk, o.ld_vk, p.n * p.K, p.D, p.B, sd, st,
-                                    "milnce dtext GEMM (MN-major G)", o.fmt_b);
+                                    "milnce dtext GEMM (MN-major G)");
         return rc;
     }
     // fp32 inputs (hi/lo planes).  Single-GPU case with B a multiple of 64: read the planes of G
@@ -968,12 +942,12 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
     int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nom);
     if (rc) return rc;
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    const Operands o = operands(p, video, text, ws);
+    const Operands o = operands(p, ws);
     const __half *vk = o.vk, *tk = o.tk;
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
     rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * o.ld_vk,
-                       o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)", o.fmt_s);
+                       o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
     if (rc) return rc;
     const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr};
     merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, 1, p.n, p.nb_r, 0, row_lse + p.i0,
@@ -993,14 +967,14 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     // workspace), 3 = both.  Split calls let the caller start the reduce-scatter of dtext
     // while dvideo is still being computed.
     int rc;
-    const Operands o = operands(p, video, text, ws);
+    const Operands o = operands(p, ws);
     const __half *vk = o.vk, *tk = o.tk;
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
     if (parts == 2) {
         tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
         return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                       "milnce dvideo GEMM (shard)", o.fmt_b);
+                                                       "milnce dvideo GEMM (shard)");
     }
     if (!reuse) {
         rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
@@ -1010,16 +984,16 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     const tc::GFast fast{&sc->g_fast, &sc->den_mid_log2};
     tc::EpiG::Params gr{den, nom, g, p.ld_g, p.BK, 1, p.i0, tc::make_fastdiv(1), 0, tc::make_fastdiv(p.K), o.inv_ss, fast};
     rc = launch_epig2(vk + (size_t)p.i0 * o.ld_vk, o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, gr,
-                                st, "milnce backward (rows-only shard) G", o.fmt_s);
+                                st, "milnce backward (rows-only shard) G");
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
     tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_video, dtext_bf16};
     rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g, p.ld_g, vk + (size_t)p.i0 * o.ld_vk, o.ld_vk, (int)p.BK, p.D, p.n, sd, st,
-                                                "milnce partial dtext GEMM (shard)", o.fmt_b);
+                                                "milnce partial dtext GEMM (shard)");
     if (rc || parts == 1) return rc;
     tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
     return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                   "milnce dvideo GEMM (shard)", o.fmt_b);
+                                                   "milnce dvideo GEMM (shard)");
 }
 
 int check_shard(const Plan &p, int dtype) {
@@ -1145,10 +1119,10 @@ extern "C" int b200head_gemm2_f16(const void *A, const void *Bm, float *C, int M
     int rc = b200::check_device();
     if (rc) return rc;
     tc::EpiStore::Params ep{C, (long long)ldc, alpha, nullptr, nullptr, 0};
-    // a_transposed: bit 0 = A passed as (Kd, M), bit 1 = Bm passed as (Kd, N), bit 2 = A holds bfloat16,
-    // bit 3 = Bm holds bfloat16
+    // a_transposed: bit 0 = A passed as (Kd, M), bit 1 = Bm passed as (Kd, N), bit 2 = BOTH operands hold
+    // bfloat16 instead of float16 (one format per instruction: mixing them faults on sm_100a)
     cudaStream_t st = (cudaStream_t)stream;
-    const uint32_t fmt = ((a_transposed & 4) ? tc::IDESC_A_BF16 : 0u) | ((a_transposed & 8) ? tc::IDESC_B_BF16 : 0u);
+    const uint32_t fmt = (a_transposed & 4) ? (tc::IDESC_A_BF16 | tc::IDESC_B_BF16) : 0u;
     switch (a_transposed & 3) {
         case 0: return launch_gemm2<tc::EpiStore, false, false>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);
         case 1: return launch_gemm2<tc::EpiStore, true, true>(A, lda, Bm, ldb, M, N, Kd, ep, st, "gemm2 test hook", fmt);

@@ -897,10 +897,9 @@ struct GemmShape {
     // kr % a_plane_rows, column offset (kr / a_plane_rows) * a_plane_cols.  0 = one plane.
     // (a_plane_rows must be a multiple of BLOCK_K.)
     int a_plane_rows, a_plane_cols;
-    // OR-ed into the instruction descriptor (CTA-pair kernels): IDESC_A_BF16 / IDESC_B_BF16 make the
-    // tensor core read that operand as bfloat16 instead of float16.  The two formats are independent,
-    // which is how the gradient GEMMs multiply the fp16 gradient tiles by the caller's bf16 embeddings
-    // without a staged fp16 copy of them.
+    // OR-ed into the instruction descriptor (CTA-pair kernels): IDESC_A_BF16 | IDESC_B_BF16 makes the
+    // tensor core read both operands as bfloat16 instead of float16.  Both or neither: an instruction
+    // with two different operand formats is rejected by the hardware (illegal instruction, measured).
     uint32_t idesc_or;
 };
 constexpr uint32_t IDESC_A_BF16 = 1u << 7, IDESC_B_BF16 = 1u << 10;

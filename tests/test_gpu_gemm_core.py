@@ -142,28 +142,24 @@ def test_gemm_cta_pair_kernel_matches_torch(M, N, Kd, transposed):
     assert err < 3e-6
 
 
-@pytest.mark.parametrize("fmt", [4, 8, 12])
 @pytest.mark.parametrize("transposed", [0, 2, 3])
-def test_gemm_cta_pair_kernel_mixed_fp16_bf16_operands(transposed, fmt):
-    """tcgen05.mma.kind::f16 takes the A and B formats separately: bit 2 of the flag makes A bfloat16,
-    bit 3 makes B bfloat16.  The bf16 loss path relies on it (bf16 x bf16 similarity tiles, fp16
-    gradient tiles x bf16 embeddings) instead of staging fp16 copies of the embeddings."""
+def test_gemm_cta_pair_kernel_bf16_operands(transposed):
+    """Bit 2 of the flag: both operands are bfloat16 (the instruction descriptor's A and B format
+    fields set to BF16).  Mixed fp16 x bf16 operands are not offered: the hardware rejects them."""
     lib = milnce_b200._lib.load()
     M, N, Kd = 512, 256, 320
-    g = torch.Generator(device="cuda").manual_seed(fmt * 10 + transposed)
-    adt = torch.bfloat16 if fmt & 4 else torch.float16
-    bdt = torch.bfloat16 if fmt & 8 else torch.float16
-    b = torch.randn((Kd, N) if transposed & 2 else (N, Kd), generator=g, device="cuda").to(bdt)
+    g = torch.Generator(device="cuda").manual_seed(40 + transposed)
+    b = torch.randn((Kd, N) if transposed & 2 else (N, Kd), generator=g, device="cuda").bfloat16()
     bt = b.float() if transposed & 2 else b.float().t()
-    a = torch.randn((Kd, M) if transposed & 1 else (M, Kd), generator=g, device="cuda").to(adt)
+    a = torch.randn((Kd, M) if transposed & 1 else (M, Kd), generator=g, device="cuda").bfloat16()
     ref = (a.float().t() if transposed & 1 else a.float()) @ bt
     c = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
     rc = lib.b200head_gemm2_f16(ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(b.data_ptr()),
                                 ctypes.c_void_p(c.data_ptr()), M, N, Kd, a.stride(0), b.stride(0),
-                                c.stride(0), ctypes.c_float(1.0), transposed | fmt,
+                                c.stride(0), ctypes.c_float(1.0), transposed | 4,
                                 milnce_b200._lib.stream_ptr())
     milnce_b200._lib.check(rc, "gemm2_f16")
     torch.cuda.synchronize()
     err = rel_err(c.cpu().numpy(), ref.cpu().numpy())
-    print(f"gemm2 mixed formats t={transposed} fmt={fmt}: rel err {err:.3e}")
+    print(f"gemm2 bf16 operands t={transposed}: rel err {err:.3e}")
     assert err < 3e-6
