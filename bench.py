@@ -340,14 +340,19 @@ def run_b200(args):
             sys.exit(3)
 
     # ---- device-resident leg (`value`) ----
-    # N = 1: forward + backward replayed as one CUDA graph through the package's GraphedMILNCEStep (the
-    # eager module is also timed and reported); N > 1: the eager GatheredMILNCELoss (NCCL inside).
-    graphed = world == 1 and not args.no_graph
+    # forward + backward replayed as one CUDA graph through the package's GraphedMILNCEStep (N = 1) or
+    # GraphedGatheredMILNCEStep (N > 1: the NCCL collectives are part of the graph); the eager module is
+    # also timed and reported.
+    graphed = not args.no_graph and (world == 1 or dtype == torch.bfloat16)
     gsteps = []
     launches_per_replay = None
     if graphed:
         n0 = launches()
-        gsteps = [milnce_b200.GraphedMILNCEStep(B, K, D, dtype=dtype, device=dev, warmup=1) for _ in range(2)]
+        if world == 1:
+            gsteps = [milnce_b200.GraphedMILNCEStep(B, K, D, dtype=dtype, device=dev, warmup=1) for _ in range(2)]
+        else:
+            gsteps = [milnce_b200.GraphedGatheredMILNCEStep(b, K, D, dtype=dtype, device=dev, scheme=args.scheme,
+                                                            warmup=1) for _ in range(2)]
         launches_per_replay = (launches() - n0) // (2 * 2)   # per instance: one warm-up pass + the capture
         with torch.no_grad():
             for gs in gsteps:
@@ -457,15 +462,17 @@ def run_b200(args):
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"MILNCELoss fwd+bwd B={B} K={K} D={D} (BASELINE configs[1])",
                    "global_batch": B, "candidates": K, "dim": D,
-                   "launch": ("one CUDA graph replay per step (GraphedMILNCEStep)" if graphed else "eager module calls"),
-                   "parallelism": (f"dp{world}: batch sharded over ranks, scheme={getattr(loss_mod, 'last_scheme', args.scheme)}"
+                   "launch": (("one CUDA graph replay per step (" + type(gsteps[0]).__name__ + ")") if graphed
+                              else "eager module calls"),
+                   "parallelism": (f"dp{world}: batch sharded over ranks, one grouped NCCL all-gather of the embeddings, "
+                                   f"scheme={getattr(loss_mod, 'last_scheme', args.scheme)}"
                                    if world > 1 else "single GPU"),
                    "l2": "per-step working set (fp16 G, 0.54 GB written and read twice) exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": pairs * args.steps / sec_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": (v_host.numel() + t_host.numel()) * v_host.element_size() * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": sec_e2e / args.steps * 1e3,
                 "pipeline": ("double-buffered inputs: the H2D copy of step i+1 overlaps step i on a copy stream"
-                             + ("; forward+backward replayed as one CUDA graph (GraphedMILNCEStep)" if graphed else ""))},
+                             + ("; forward+backward replayed as one CUDA graph" if graphed else ""))},
         "gpu_launches": int(gpu_launches),
         "gpu_launches_how": ("b200head_launch_count() over the graph capture x replays" if graphed
                              else "b200head_launch_count() difference over warm-up + timed steps, scaled to the timed steps"),
@@ -511,6 +518,8 @@ def run_b200(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         os.dup2(2, 1)
+        for gs in gsteps:
+            gs.close()
         dist.destroy_process_group()
 
 

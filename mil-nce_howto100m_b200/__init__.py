@@ -6,6 +6,7 @@ Drop-ins for the reference's ``loss.MILNCELoss``, ``soft_dtw_cuda.SoftDTW`` and
 from . import _lib
 from .loss import GraphedMILNCEStep, MILNCELoss
 from .soft_dtw_cuda import SoftDTW
-from .utils import AllGather, GatheredMILNCELoss
+from .utils import AllGather, GatheredMILNCELoss, GraphedGatheredMILNCEStep
 
-__all__ = ["MILNCELoss", "GraphedMILNCEStep", "SoftDTW", "AllGather", "GatheredMILNCELoss", "_lib"]
+__all__ = ["MILNCELoss", "GraphedMILNCEStep", "SoftDTW", "AllGather", "GatheredMILNCELoss",
+           "GraphedGatheredMILNCEStep", "_lib"]

@@ -94,6 +94,36 @@ int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t
     return 0;
 }
 
+// fp32 tensor (inner, rows, batch), dense: box = 32 floats (128 bytes) x box_rows x 1, SWIZZLE_128B with
+// 16-byte atoms, or with 32-byte atoms when atom32 != 0 (what an MN-major tf32 UMMA operand needs).
+// Rows or columns of a box that fall outside the tensor are zero-filled.
+int make_tmap_3d_f32(CUtensorMap *map, const void *base, uint64_t inner, uint64_t rows, uint64_t batch,
+                     uint32_t box_rows, int atom32) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return B200HEAD_ERR_CUDA;
+    }
+    if (((uintptr_t)base & 15) || ((inner * 4) & 15)) {
+        set_error("TMA operand must be 16-byte aligned with a 16-byte multiple row pitch (base=%p inner=%llu)",
+                  base, (unsigned long long)inner);
+        return B200HEAD_ERR_ARG;
+    }
+    cuuint64_t gdim[3] = {inner, rows, batch};
+    cuuint64_t gstr[2] = {inner * 4, inner * rows * 4};
+    cuuint32_t box[3] = {32, box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void *>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (3-D fp32) failed with CUresult %d (inner=%llu rows=%llu batch=%llu)",
+                  (int)r, (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)batch);
+        return B200HEAD_ERR_CUDA;
+    }
+    return 0;
+}
+
 }  // namespace b200
 
 extern "C" const char *b200head_last_error(void) { return b200::get_error(); }

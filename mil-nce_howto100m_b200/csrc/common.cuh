@@ -24,6 +24,11 @@ int check_device();
 int make_tmap_2d_f16(CUtensorMap *map, const void *base, uint64_t rows, uint64_t cols,
                      uint64_t ld, uint32_t box_rows);
 
+// fp32 tensor (inner, rows, batch): box = 32 floats (128 bytes) x box_rows x 1, zero fill; 128-byte
+// swizzle with 16-byte atoms (atom32 == 0) or 32-byte atoms (atom32 != 0)
+int make_tmap_3d_f32(CUtensorMap *map, const void *base, uint64_t inner, uint64_t rows, uint64_t batch,
+                     uint32_t box_rows, int atom32);
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Launch with programmatic stream serialization: the grid may be scheduled while the previous

@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "sdtw_fused.cuh"
+#include "sdtw_tc.cuh"
 
 namespace {
 
@@ -30,7 +31,7 @@ using b200::align_up;
 constexpr float COS_EPS = 1e-8f;  // torch cosine_similarity eps (soft_dtw_cuda.py:347)
 
 struct AuxPlan {
-    // cell (N+M-1, N) float4 per pair, diagonal-major: {w_diag, w_up, w_left, D}
+    // cell (M, N) float4 per pair, [j][i] (i contiguous): {w_diag, w_up, w_left, D}
     // acoef (B,N,M): GEMM coefficient of the input gradient, scoef (B,N,M): summand of the
     // "own vector" coefficient; nx (B,N), ny (B,M) norms; rsum (B,N), csum (B,M)
     size_t off_cell, off_d, off_acoef, off_nx, off_ny, off_rsum, off_csum, off_flag, total;
@@ -40,7 +41,7 @@ AuxPlan make_aux(int B, int N, int M) {
     AuxPlan a;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
-    a.off_cell = take((size_t)B * (N + M - 1) * N * sizeof(float4));
+    a.off_cell = take((size_t)B * N * M * sizeof(float4));
     a.off_d = take((size_t)B * N * M * 4);
     a.off_acoef = take((size_t)B * N * M * 4);
     a.off_nx = take((size_t)B * N * 4);
@@ -185,7 +186,7 @@ __global__ void dp_fwd_kernel(const float *__restrict__ D, int N, int M, float g
     const double inv_g = 1.0 / g;
     const float *Db = D + (size_t)b * N * M;
     float *Rb = Rout ? Rout + (size_t)b * (N + 2) * (M + 2) : nullptr;
-    float4 *cb = cell ? cell + (size_t)b * (N + M - 1) * N : nullptr;
+    float4 *cb = cell ? cell + (size_t)b * N * M : nullptr;
 
     if (Rb) {  // border of the (N+2, M+2) array exactly as the reference initialises it
         for (int e = i; e < (N + 2) * (M + 2); e += T) {
@@ -228,7 +229,7 @@ __global__ void dp_fwd_kernel(const float *__restrict__ D, int N, int M, float g
                 }
             }
             if (Rb) Rb[(size_t)(i + 1) * (M + 2) + (j + 1)] = (float)rnew;
-            if (cb) cb[(size_t)p * N + i] = w;
+            if (cb) cb[(size_t)j * N + i] = w;
             diag = up;   // becomes R[i-1, j] = diagonal neighbour of the next column
             left = rnew;
             if (i == N - 1 && j == M - 1) out[b] = (float)rnew;
@@ -251,7 +252,7 @@ __global__ void dp_bwd_kernel(const float4 *__restrict__ cell, const float *__re
     float2 *pb0 = reinterpret_cast<float2 *>(sh_f);
     float2 *pb1 = pb0 + (T + 1);
     float *scs = reinterpret_cast<float *>(pb1 + (T + 1));
-    const float4 *cb = cell + (size_t)b * (N + M - 1) * N;
+    const float4 *cb = cell + (size_t)b * N * M;
     const float go = grad_out[b];
     for (int e = i; e < 2 * (T + 1); e += T) pb0[e] = make_float2(0.f, 0.f);
     for (int e = i; e < M; e += T) scs[e] = 0.f;
@@ -268,7 +269,7 @@ __global__ void dp_bwd_kernel(const float4 *__restrict__ cell, const float *__re
         float2 pub = make_float2(0.f, 0.f);
         if (active) {
             const float2 below = prev[i + 1];  // cell (i+1, j): {E*w_up, E*w_diag}
-            const float4 w = cb[(size_t)p * N + i];
+            const float4 w = cb[(size_t)j * N + i];
             const bool pruned = (bandwidth > 0.f) && (fabsf((float)(i - j)) > bandwidth);
             float e = 0.f;
             if (!pruned) {
@@ -471,29 +472,31 @@ extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M,
     int *flag = reinterpret_cast<int *>(ax + a.off_flag);
     const int *run_if = nullptr;
     if (fused::eligible(N, M, d, dist_kind, gamma, x, y)) {
-        // short sequences: one fused kernel per pair (tensor-core distance tile + wavefront)
+        // short sequences: one fused kernel per pair (tcgen05 distance tile + wavefront)
         float4 *cellp = reinterpret_cast<float4 *>(ax + a.off_cell);
+        // exp(1 - cos) is bounded and eligible() has checked gamma; negative_dot distances are not:
+        // the kernel raises `flag` when |D| / gamma is beyond its scaled-pair exponents, and the general
+        // kernels below then redo the batch (they exit at once when the flag is clear)
+        int *fl = (dist_kind == B200HEAD_DIST_COSINE) ? nullptr : flag;
+        if (fl) B200_CUDA_OK(cudaMemsetAsync(fl, 0, sizeof(int), st));
+#ifdef SDTW_FWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing
         const int smem = (int)sizeof(fused::FwdSmem);
-        if (dist_kind == B200HEAD_DIST_COSINE) {
-            // exp(1 - cos) is bounded: eligible() has already checked gamma, no device-side guard needed
-            B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<0>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            fused::fwd_kernel<0><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
-                                                       nx, ny, nullptr);
-            b200::note_launches(1);
-        B200_LAUNCH_OK("sdtw fused forward kernel");
-            return 0;
-        }
-        // negative_dot distances are unbounded: the kernel raises `flag` when |D| / gamma is beyond its
-        // scaled-pair exponents, and the general kernels below then redo the batch (they exit at
-        // once when the flag is clear)
-        B200_CUDA_OK(cudaMemsetAsync(flag, 0, sizeof(int), st));
-        B200_CUDA_OK(cudaFuncSetAttribute(fused::fwd_kernel<1>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        fused::fwd_kernel<1><<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp,
-                                                   nx, ny, flag);
+        auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? fused::fwd_kernel<0> : fused::fwd_kernel<1>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        kern<<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl);
+#else
+        CUtensorMap mx, my;
+        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)B, sdtc::T, 0);
+        if (rc) return rc;
+        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)B, sdtc::T, 0);
+        if (rc) return rc;
+        auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? sdtc::fwd_kernel<0> : sdtc::fwd_kernel<1>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sdtc::FWD_SMEM));
+        kern<<<B, sdtc::THREADS, sdtc::FWD_SMEM, st>>>(mx, my, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl);
+#endif
         b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused forward kernel");
+        if (fl == nullptr) return 0;
         run_if = flag;
     }
     return general_forward(x, y, B, N, M, d, gamma, bandwidth, dist_kind, R, out, Dm, nx, ny,
@@ -525,18 +528,21 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     float *rsum = reinterpret_cast<float *>(ax + a.off_rsum);
     float *csum = reinterpret_cast<float *>(ax + a.off_csum);
     if (fused::eligible(N, M, d, dist_kind, gamma, x, y)) {
+#ifdef SDTW_BWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing
         const int smem = (int)sizeof(fused::BwdSmem);
-        if (dist_kind == B200HEAD_DIST_COSINE) {
-            B200_CUDA_OK(cudaFuncSetAttribute(fused::bwd_kernel<0>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            fused::bwd_kernel<0><<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E,
-                                                       dx, dy);
-        } else {
-            B200_CUDA_OK(cudaFuncSetAttribute(fused::bwd_kernel<1>,
-                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            fused::bwd_kernel<1><<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E,
-                                                       dx, dy);
-        }
+        auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? fused::bwd_kernel<0> : fused::bwd_kernel<1>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        kern<<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx, dy);
+#else
+        CUtensorMap mx, my;
+        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)B, sdtc::T, 1);
+        if (rc) return rc;
+        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)B, sdtc::T, 1);
+        if (rc) return rc;
+        auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? sdtc::bwd_kernel<0> : sdtc::bwd_kernel<1>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sdtc::BWD_SMEM));
+        kern<<<B, sdtc::THREADS, sdtc::BWD_SMEM, st>>>(mx, my, x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx, dy);
+#endif
         b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused backward kernel");
         return 0;
@@ -654,6 +660,6 @@ extern "C" int sdtw_forward_noalloc(const float *x, const float *y, int B, int N
 
 #ifdef SDTW_PROFILE
 extern "C" int sdtw_debug_read(long long *host16) {
-    return (int)cudaMemcpyFromSymbol(host16, fused::g_prof, sizeof(long long) * 16);
+    return (int)cudaMemcpyFromSymbol(host16, fused::g_prof, sizeof(long long) * 32);
 }
 #endif

@@ -24,7 +24,7 @@ namespace fused {
 
 #ifdef SDTW_PROFILE
 // developer-only phase timestamps (block 0): build with -DSDTW_PROFILE, read with sdtw_debug_read
-__device__ long long g_prof[16];
+__device__ long long g_prof[32];
 #define SDTW_STAMP(k)                                                  \
     do {                                                               \
         if (blockIdx.x == 0 && threadIdx.x == 0) g_prof[k] = clock64(); \
@@ -381,7 +381,7 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
     // ---- all threads: soft-min weights (for the backward), R and the result, diagonal by diagonal
     {
         const float g_ln2 = gamma * 0.6931471805599453f;
-        float4 *cb = cell ? cell + (size_t)b * (N + M - 1) * N : nullptr;
+        float4 *cb = cell ? cell + (size_t)b * N * M : nullptr;   // [j][i]
         const PVal zero = {0.f, E_ZERO};
         const int i = tid & 63;
         for (int p = tid >> 6; p < steps; p += 4) {
@@ -395,7 +395,7 @@ fwd_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int 
             const bool ok = !((bandwidth > 0.f) && (fabsf((float)(i - j)) > bandwidth));
             float4 w = make_float4(0.f, 0.f, 0.f, s.Dt[i][j]);
             (void)sdtw_cell(a, bb, c, s.Wf[i][j], s.We[i][j], ok, w.x, w.y, w.z);
-            if (cb) cb[(size_t)p * N + i] = w;
+            if (cb) cb[(size_t)j * N + i] = w;
             if (Rb != nullptr || (i == N - 1 && j == M - 1)) {
                 const float pf = Pf[i][j];
                 const float Rv = (pf > 0.f) ? -g_ln2 * (lg2_approx(pf) + (float)Pe[i][j]) : INFINITY;
@@ -452,7 +452,7 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
     // Warp 1 (rows 32..63) leads; warp 0 reads row 32's products from a per-step mailbox.
     if (warp < 2) {
         const int r = tid;
-        const float4 *cb = cell + (size_t)b * (N + M - 1) * N;
+        const float4 *cb = cell + (size_t)b * N * M;   // [j][i]
         const int steps = N + M - 1;
         volatile unsigned long long *mb = s.mb;
         float left = 0.f;             // E[r, j+1] * w_left(r, j+1)
@@ -475,7 +475,7 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
         //    out-of-range cells are zero (the forward stores zeros, cp.async zero-fills), so their
         //    E comes out as 0.
         const unsigned mrow = (r < N) ? (unsigned)M : 0u;       // (unsigned)j < mrow  <=>  cell (r, j) exists
-        const float4 *src = cb + (size_t)(steps - 1) * N + r;   // weights of the step being fetched
+        const float4 *src = cb + ((long long)(steps - 1) - r) * N + r;   // weights of cell (r, p - r) of the step being fetched
         const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(&s.wring[0][r]);
         auto fetch_w = [&](int p, int slot) {                   // slot is a compile-time constant at every call
             const bool okw = (unsigned)(p - r) < mrow;
@@ -536,7 +536,7 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
     __syncthreads();
     // ---- all threads: E -> coefficient tile A (and, for cosine, the summand tile S = A * c) ----
     {
-        const float4 *cb = cell + (size_t)b * (N + M - 1) * N;
+        const float4 *cb = cell + (size_t)b * N * M;
         const float go = grad_out[b];
         float(*S)[BS] = s.xs[1];  // stage 1 of the ring is not in flight yet
         const int steps = N + M - 1;
@@ -548,7 +548,7 @@ bwd_kernel(const float *__restrict__ x, const float *__restrict__ y, const float
             if (Eout) Eout[((size_t)b * N + i) * M + j] = e;
             const float gE = go * e;
             if (KIND == 0) {
-                const float dd = cb[(size_t)p * N + i].w;
+                const float dd = cb[(size_t)j * N + i].w;
                 const float a = -gE * dd;                                      // d loss / d cos  (D = exp(1 - c))
                 s.A[i][j] = a;
                 S[i][j] = a * (1.f - 0.6931471805599453f * lg2_approx(dd));   // times c = 1 - ln D

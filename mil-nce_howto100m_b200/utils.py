@@ -227,3 +227,62 @@ class GatheredMILNCELoss(torch.nn.Module):
         fn = _GatheredMILNCERows if use_rows else _GatheredMILNCE
         opts = {"marks": self._marks, "partial_dtype": self.partial_dtype}
         return fn.apply(video_embd, text_embd, world, rank, self.group, backend, opts)
+
+
+class GraphedGatheredMILNCEStep:
+    """One sharded loss step - embedding all-gather, sharded forward, backward, gradient exchange -
+    for fixed local shapes, captured ONCE as a CUDA graph (NCCL collectives included) and replayed.
+
+    From two ranks on, a step is a few hundred microseconds of GPU work behind some forty host-side
+    operations (launches, allocations, NCCL calls, autograd), and the eager module is bound by the
+    host.  Replaying removes that time from every step.  Same contract as GraphedMILNCEStep:
+
+        step = GraphedGatheredMILNCEStep(b, K, D)        # every rank, same arguments; captures
+        loss, dvideo, dtext = step(video_local, text_local)
+        ...
+        step.close()                                      # before destroy_process_group()
+
+    Outputs are the graph's static tensors (overwritten by the next replay): the global loss and
+    d loss / d(local embeddings), i.e. what AllGather.backward (reference utils.py:20-24) hands back.
+    All ranks must construct, replay and close in step with each other (the graph holds collectives).
+    """
+
+    def __init__(self, b, K, D, dtype=torch.bfloat16, device=None, group=None, scheme="auto",
+                 partial_dtype=None, warmup=3):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.video = torch.zeros(b, D, dtype=dtype, device=dev).requires_grad_(True)
+        self.text = torch.zeros(b * K, D, dtype=dtype, device=dev).requires_grad_(True)
+        self.module = GatheredMILNCELoss(group=group, scheme=scheme, partial_dtype=partial_dtype)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):       # warm-up off the capture: communicators, library, allocator
+            for _ in range(max(1, warmup)):
+                self.video.grad = None
+                self.text.grad = None
+                self.module(self.video, self.text).backward()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.video.grad = None
+        self.text.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self.module(self.video, self.text)
+            self.loss.backward()
+        self.dvideo = self.video.grad
+        self.dtext = self.text.grad
+
+    def replay(self):
+        self.graph.replay()
+        return self.loss, self.dvideo, self.dtext
+
+    def __call__(self, video_embd, text_embd):
+        with torch.no_grad():
+            self.video.copy_(video_embd, non_blocking=True)
+            self.text.copy_(text_embd, non_blocking=True)
+        return self.replay()
+
+    def close(self):
+        """Release the captured graph (it pins NCCL work); call on every rank before the process
+        group is destroyed."""
+        torch.cuda.synchronize()
+        self.graph = None

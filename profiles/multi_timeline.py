@@ -83,7 +83,24 @@ def main():
         mod._marks = None
         med = [sorted(per_phase[k])[len(per_phase[k]) // 2] for k in order]
         med = allmax(med)
-        lines.append(f"\n## {name}: whole step {whole:.0f} us (back to back, no stamps)")
+        # the same step captured as one CUDA graph (GraphedGatheredMILNCEStep) and replayed
+        gs = milnce_b200.GraphedGatheredMILNCEStep(b, K, D, **kw)
+        with torch.no_grad():
+            gs.video.copy_(v)
+            gs.text.copy_(t)
+        for _ in range(3):
+            gs.replay()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(args.steps):
+            gs.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        graphed = allmax([e0.elapsed_time(e1) / args.steps * 1e3])[0]
+        gs.close()
+        lines.append(f"\n## {name}: whole step {whole:.0f} us eager, {graphed:.0f} us replayed as one CUDA graph "
+                     f"(back to back, no stamps)")
         for k, m in zip(order, med):
             note = "   (autograd glue between forward and backward; host-side)" if k == "backward_start" else ""
             lines.append(f"  {k:34s} {m:8.0f}{note}")

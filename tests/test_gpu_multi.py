@@ -67,3 +67,49 @@ def test_gathered_loss_two_gpus_nccl(scheme):
     out = mp.get_context("spawn").Array("i", [0] * world)
     mp.spawn(_worker, args=(world, _free_port(), scheme, out), nprocs=world, join=True)
     assert list(out) == [1] * world
+
+
+def _worker_graphed(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import milnce_b200
+        B, K, D = 1024, 4, 512
+        b = B // world
+        step = milnce_b200.GraphedGatheredMILNCEStep(b, K, D, scheme="rows", partial_dtype=torch.bfloat16)
+        ok = True
+        for seed in (5, 6):     # two replays on different inputs
+            g = torch.Generator().manual_seed(seed)
+            V = (torch.randn(B, D, generator=g) * 0.1).bfloat16().cuda()
+            T = (torch.randn(B * K, D, generator=g) * 0.1).bfloat16().cuda()
+            loss, dv, dt = step(V[rank * b:(rank + 1) * b], T[rank * b * K:(rank + 1) * b * K])
+            Vf = V.clone().requires_grad_(True)
+            Tf = T.clone().requires_grad_(True)
+            ref = milnce_b200.MILNCELoss()(Vf, Tf)
+            ref.backward()
+            torch.cuda.synchronize()
+            dv_ref = Vf.grad[rank * b:(rank + 1) * b].float()
+            dt_ref = Tf.grad[rank * b * K:(rank + 1) * b * K].float()
+            e1 = ((dv.float() - dv_ref).norm() / dv_ref.norm()).item()
+            e2 = ((dt.float() - dt_ref).norm() / dt_ref.norm()).item()
+            good = abs(loss.item() - ref.item()) < 1e-5 * abs(ref.item()) and e1 < 5e-3 and e2 < 5e-3
+            if not good:
+                print(f"rank {rank} seed {seed}: loss {loss.item()} vs {ref.item()} dV {e1} dT {e2}", flush=True)
+            ok = ok and good
+        step.close()
+        out[rank] = 1 if ok else 0
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.timeout(240)
+def test_graphed_gathered_step_two_gpus_nccl():
+    """The whole sharded step, NCCL collectives included, captured as one CUDA graph and replayed."""
+    world = 2
+    out = mp.get_context("spawn").Array("i", [0] * world)
+    mp.spawn(_worker_graphed, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert list(out) == [1] * world
