@@ -58,6 +58,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true", help="time the eager module instead of the CUDA graph")
     ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s sustained-regime leg")
     ap.add_argument("--cpu-budget-s", type=float, default=150.0, help="wall-clock budget of the reference arm")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 5],
+                    help="2: the loss head alone (the headline, BASELINE configs[1..3]); 5: the S3D-G train step of "
+                         "configs[4] with both loss heads (harness/config5.py; needs oracle/_ref)")
     return ap.parse_args()
 
 
@@ -635,6 +638,12 @@ def bench_sdtw(dev, pk, args, world, rank, barrier, max_over_ranks):
 
 def main():
     args = parse()
+    if args.config == 5:
+        sys.argv = [os.path.join(ROOT, "harness", "config5.py"), "--steps", str(max(2, min(args.steps, 6))),
+                    "--warmup", str(max(1, min(args.warmup, 2)))]
+        import runpy
+        runpy.run_path(sys.argv[0], run_name="__main__")
+        return
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -149,6 +149,24 @@ int sdtw_backward(const float *x, const float *y, const float *grad_out,
                   const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
                   void *stream);
 
+/* The same on INDEX PAIRS: pair p compares sequence ix[p] of the x bank (Bx, N, d) with sequence iy[p]
+ * of the y bank (By, M, d); ix / iy are device int32 arrays of length P, or NULL for the identity (that
+ * bank must then hold exactly P sequences).  This is how the reference's composite losses are served
+ * without materialising their operand copies: SDTW_3 builds all b*b pairs by
+ * expand(b, b, n, d).reshape(-1, n, d) (reference loss.py:101-105, 112-116, 123-127), CDTW repeats one
+ * sequence 8 times (loss.py:29).  out[P], R (P, N+2, M+2) and aux (sdtw_aux_bytes(P, N, M, d)) are per
+ * pair.  In the backward the gradient of a sequence is the SUM over the pairs it takes part in: dx
+ * (Bx, N, d) and dy (By, M, d) are zeroed by the call and accumulated with atomic adds when an index
+ * list is given (summation order, hence the last float32 bits, then varies from run to run); dx and dy
+ * must not overlap.  E (P, N, M) optional as in sdtw_backward. */
+int sdtw_forward_pairs(const float *x, int Bx, const float *y, int By, const int *ix, const int *iy, int P,
+                       int N, int M, int d, float gamma, float bandwidth, int dist_kind,
+                       float *R, float *out, void *aux, size_t aux_bytes, void *stream);
+int sdtw_backward_pairs(const float *x, int Bx, const float *y, int By, const int *ix, const int *iy, int P,
+                        const float *grad_out, int N, int M, int d, float gamma, float bandwidth,
+                        int dist_kind, const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
+                        void *stream);
+
 /* Forward for callers that cannot allocate device memory at all.  It has no
  * counterpart in the reference (there the scratch is torch tensors,
  * soft_dtw_cuda.py:135-136).  Same arguments and results as sdtw_forward, minus

@@ -107,6 +107,11 @@ def _declare(lib):
     lib.sdtw_backward.restype = i32
     lib.sdtw_backward.argtypes = [fp, fp, fp, i32, i32, i32, i32, f32, f32, i32, vp, sz, fp, fp, fp,
                                   vp]
+    lib.sdtw_forward_pairs.restype = i32
+    lib.sdtw_forward_pairs.argtypes = [fp, i32, fp, i32, vp, vp, i32, i32, i32, i32, f32, f32, i32, fp, fp, vp, sz, vp]
+    lib.sdtw_backward_pairs.restype = i32
+    lib.sdtw_backward_pairs.argtypes = [fp, i32, fp, i32, vp, vp, i32, fp, i32, i32, i32, f32, f32, i32, vp, sz, fp,
+                                        fp, fp, vp]
     lib.sdtw_forward_noalloc.restype = i32
     lib.sdtw_forward_noalloc.argtypes = [fp, fp, i32, i32, i32, i32, f32, f32, i32, fp, fp, vp]
     lib.b200head_gemm_tn_f16.restype = i32

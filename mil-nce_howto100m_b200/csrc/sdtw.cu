@@ -63,7 +63,7 @@ template <int KIND>
 __global__ void __launch_bounds__(256)
 dist_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int M, int d,
             float *__restrict__ Dout, float *__restrict__ nx_out, float *__restrict__ ny_out,
-            const int *__restrict__ run_if) {
+            const int *__restrict__ run_if, const int *__restrict__ ix, const int *__restrict__ iy) {
     // run_if: device flag; the grid exits at once when it is 0 (the fused kernel handled the batch)
     if (run_if != nullptr && *run_if == 0) return;
     __shared__ float xs[DK][DT + 4];
@@ -73,8 +73,8 @@ dist_kernel(const float *__restrict__ x, const float *__restrict__ y, int N, int
     const int i0 = blockIdx.y * DT, j0 = blockIdx.x * DT;
     const int tid = threadIdx.x;
     const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 threads, 4 x 4 cells each
-    const float *xb = x + (size_t)b * N * d;
-    const float *yb = y + (size_t)b * M * d;
+    const float *xb = x + (size_t)(ix ? ix[b] : b) * N * d;   // pair b = (x sequence ix[b], y sequence iy[b])
+    const float *yb = y + (size_t)(iy ? iy[b] : b) * M * d;
     float acc[4][4] = {};
     float nxa[4] = {}, nya[4] = {};
     // loader mapping: 64 rows x 32 features = 512 float4; two per thread
@@ -313,13 +313,17 @@ __global__ void __launch_bounds__(256)
 grad_kernel(const float *__restrict__ acoef, long long sr, long long sq, int R, int Q, int d,
             const float *__restrict__ src, const float *__restrict__ self,
             const float *__restrict__ norm_r, const float *__restrict__ norm_q,
-            const float *__restrict__ sum_r, float *__restrict__ out) {
+            const float *__restrict__ sum_r, float *__restrict__ out, const int *__restrict__ iq,
+            const int *__restrict__ ir, int accumulate) {
+    // iq / ir: the pair's sequence in the bank `src` is read from / `self` and `out` belong to (identity when
+    // null); accumulate: several pairs may share an output sequence (atomic adds, out zeroed by the host)
     __shared__ float as[GQ][GR + 4];
     __shared__ float ss[GQ][GD + 4];
     const int b = blockIdx.z, r0 = blockIdx.y * GR, d0 = blockIdx.x * GD;
     const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
     const float *ab = acoef + (size_t)b * R * Q;  // R*Q == N*M either way
-    const float *sb = src + (size_t)b * Q * d;
+    const int bq = iq ? iq[b] : b, br = ir ? ir[b] : b;
+    const float *sb = src + (size_t)bq * Q * d;
     const float *nq = norm_q ? norm_q + (size_t)b * Q : nullptr;
     float acc[4][4] = {};
     for (int q0 = 0; q0 < Q; q0 += GQ) {
@@ -379,10 +383,11 @@ grad_kernel(const float *__restrict__ acoef, long long sr, long long sq, int R, 
             if (gd >= d) continue;
             float v = acc[p][q] * rscale;
             if (KIND != B200HEAD_DIST_NEGATIVE_DOT) {
-                const float sv = self[((size_t)b * R + gr) * d + gd];
-                v = (KIND == B200HEAD_DIST_EUCLIDEAN) ? fmaf(own, sv, v) : fmaf(own, sv, v);
+                const float sv = self[((size_t)br * R + gr) * d + gd];
+                v = fmaf(own, sv, v);
             }
-            out[((size_t)b * R + gr) * d + gd] = v;
+            if (accumulate) atomicAdd(&out[((size_t)br * R + gr) * d + gd], v);
+            else out[((size_t)br * R + gr) * d + gd] = v;
         }
     }
 }
@@ -391,14 +396,15 @@ grad_kernel(const float *__restrict__ acoef, long long sr, long long sq, int R, 
 // null): when given and zero, both grids exit immediately.
 int general_forward(const float *x, const float *y, int B, int N, int M, int d, float gamma, float bandwidth,
                     int dist_kind, float *R, float *out, float *Dm, float *nx, float *ny, float4 *cell,
-                    const int *run_if, cudaStream_t st, const char *who) {
+                    const int *run_if, cudaStream_t st, const char *who, const int *ix = nullptr,
+                    const int *iy = nullptr) {
     dim3 grid((M + DT - 1) / DT, (N + DT - 1) / DT, B);
     if (dist_kind == B200HEAD_DIST_COSINE)
-        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+        dist_kernel<B200HEAD_DIST_COSINE><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if, ix, iy);
     else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT)
-        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+        dist_kernel<B200HEAD_DIST_NEGATIVE_DOT><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if, ix, iy);
     else
-        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if);
+        dist_kernel<B200HEAD_DIST_EUCLIDEAN><<<grid, 256, 0, st>>>(x, y, N, M, d, Dm, nx, ny, run_if, ix, iy);
     const int T = std::max(32, (N + 31) / 32 * 32);
     const size_t sh = 2 * (size_t)(T + 1) * sizeof(double);
     dp_fwd_kernel<<<B, T, sh, st>>>(Dm, N, M, gamma, bandwidth, R, out, cell, run_if);
@@ -449,22 +455,24 @@ extern "C" size_t sdtw_aux_bytes(int B, int N, int M, int d) {
     return make_aux(B, N, M).total;
 }
 
-extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M, int d, float gamma,
-                            float bandwidth, int dist_kind, float *R, float *out, void *aux,
-                            size_t aux_bytes, void *stream) {
-    int rc = check_args("sdtw_forward", x, y, B, N, M, d, gamma, dist_kind);
+namespace {
+
+// P pairs; pair p compares sequence ix[p] of the x bank (Bx sequences) with sequence iy[p] of the y bank
+// (By sequences); ix == iy == nullptr is the plain batched case (P == Bx == By, pair p = (p, p)).
+int forward_impl(const char *who, const float *x, int Bx, const float *y, int By, const int *ix, const int *iy,
+                 int P, int N, int M, int d, float gamma, float bandwidth, int dist_kind, float *R, float *out,
+                 void *aux, size_t aux_bytes, cudaStream_t st) {
+    int rc = check_args(who, x, y, P, N, M, d, gamma, dist_kind);
     if (rc) return rc;
     if (!out) {
-        b200::set_error("sdtw_forward: out is null");
+        b200::set_error("%s: out is null", who);
         return B200HEAD_ERR_ARG;
     }
-    const AuxPlan a = make_aux(B, N, M);
+    const AuxPlan a = make_aux(P, N, M);
     if (!aux || aux_bytes < a.total || ((uintptr_t)aux & 255)) {
-        b200::set_error("sdtw_forward: aux must be 256-byte aligned and >= %zu bytes (got %zu)",
-                        a.total, aux_bytes);
+        b200::set_error("%s: aux must be 256-byte aligned and >= %zu bytes (got %zu)", who, a.total, aux_bytes);
         return B200HEAD_ERR_WS;
     }
-    cudaStream_t st = (cudaStream_t)stream;
     uint8_t *ax = (uint8_t *)aux;
     float *Dm = reinterpret_cast<float *>(ax + a.off_d);
     float *nx = reinterpret_cast<float *>(ax + a.off_nx);
@@ -479,47 +487,45 @@ extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M,
         // kernels below then redo the batch (they exit at once when the flag is clear)
         int *fl = (dist_kind == B200HEAD_DIST_COSINE) ? nullptr : flag;
         if (fl) B200_CUDA_OK(cudaMemsetAsync(fl, 0, sizeof(int), st));
-#ifdef SDTW_FWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing
+#ifdef SDTW_FWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing (no index lists)
         const int smem = (int)sizeof(fused::FwdSmem);
         auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? fused::fwd_kernel<0> : fused::fwd_kernel<1>;
         B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        kern<<<B, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl);
+        kern<<<P, 256, smem, st>>>(x, y, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl);
 #else
         CUtensorMap mx, my;
-        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)B, sdtc::T, 0);
+        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)Bx, sdtc::T, 0);
         if (rc) return rc;
-        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)B, sdtc::T, 0);
+        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)By, sdtc::T, 0);
         if (rc) return rc;
         auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? sdtc::fwd_kernel<0> : sdtc::fwd_kernel<1>;
         B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sdtc::FWD_SMEM));
-        kern<<<B, sdtc::THREADS, sdtc::FWD_SMEM, st>>>(mx, my, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl);
+        kern<<<P, sdtc::THREADS, sdtc::FWD_SMEM, st>>>(mx, my, N, M, d, gamma, bandwidth, R, out, cellp, nx, ny, fl,
+                                                       ix, iy);
 #endif
         b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused forward kernel");
         if (fl == nullptr) return 0;
         run_if = flag;
     }
-    return general_forward(x, y, B, N, M, d, gamma, bandwidth, dist_kind, R, out, Dm, nx, ny,
-                           reinterpret_cast<float4 *>(ax + a.off_cell), run_if, st, "sdtw_forward");
+    return general_forward(x, y, P, N, M, d, gamma, bandwidth, dist_kind, R, out, Dm, nx, ny,
+                           reinterpret_cast<float4 *>(ax + a.off_cell), run_if, st, who, ix, iy);
 }
 
-extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_out, int B, int N,
-                             int M, int d, float gamma, float bandwidth, int dist_kind,
-                             const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
-                             void *stream) {
-    int rc = check_args("sdtw_backward", x, y, B, N, M, d, gamma, dist_kind);
+int backward_impl(const char *who, const float *x, int Bx, const float *y, int By, const int *ix, const int *iy,
+                  int P, const float *grad_out, int N, int M, int d, float gamma, float bandwidth, int dist_kind,
+                  const void *aux, size_t aux_bytes, float *E, float *dx, float *dy, cudaStream_t st) {
+    int rc = check_args(who, x, y, P, N, M, d, gamma, dist_kind);
     if (rc) return rc;
     if (!grad_out || !dx || !dy) {
-        b200::set_error("sdtw_backward: null pointer argument");
+        b200::set_error("%s: null pointer argument", who);
         return B200HEAD_ERR_ARG;
     }
-    const AuxPlan a = make_aux(B, N, M);
+    const AuxPlan a = make_aux(P, N, M);
     if (!aux || aux_bytes < a.total || ((uintptr_t)aux & 255)) {
-        b200::set_error("sdtw_backward: aux must be the buffer sdtw_forward filled (>= %zu bytes)",
-                        a.total);
+        b200::set_error("%s: aux must be the buffer the forward filled (>= %zu bytes)", who, a.total);
         return B200HEAD_ERR_WS;
     }
-    cudaStream_t st = (cudaStream_t)stream;
     uint8_t *ax = (uint8_t *)const_cast<void *>(aux);
     const float4 *cell = reinterpret_cast<const float4 *>(ax + a.off_cell);
     float *acoef = reinterpret_cast<float *>(ax + a.off_acoef);
@@ -527,21 +533,27 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     float *ny = reinterpret_cast<float *>(ax + a.off_ny);
     float *rsum = reinterpret_cast<float *>(ax + a.off_rsum);
     float *csum = reinterpret_cast<float *>(ax + a.off_csum);
+    const int accumulate = (ix || iy) ? 1 : 0;
+    if (accumulate) {   // several pairs may share a sequence: gradients are accumulated with atomic adds
+        B200_CUDA_OK(cudaMemsetAsync(dx, 0, (size_t)Bx * N * d * sizeof(float), st));
+        if (dy != dx) B200_CUDA_OK(cudaMemsetAsync(dy, 0, (size_t)By * M * d * sizeof(float), st));
+    }
     if (fused::eligible(N, M, d, dist_kind, gamma, x, y)) {
-#ifdef SDTW_BWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing
+#ifdef SDTW_BWD_LEGACY   // variant builds: the mma.sync kernel of round 1, for A/B timing (no index lists)
         const int smem = (int)sizeof(fused::BwdSmem);
         auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? fused::bwd_kernel<0> : fused::bwd_kernel<1>;
         B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        kern<<<B, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx, dy);
+        kern<<<P, 256, smem, st>>>(x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx, dy);
 #else
         CUtensorMap mx, my;
-        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)B, sdtc::T, 1);
+        rc = b200::make_tmap_3d_f32(&mx, x, (uint64_t)d, (uint64_t)N, (uint64_t)Bx, sdtc::T, 1);
         if (rc) return rc;
-        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)B, sdtc::T, 1);
+        rc = b200::make_tmap_3d_f32(&my, y, (uint64_t)d, (uint64_t)M, (uint64_t)By, sdtc::T, 1);
         if (rc) return rc;
         auto kern = (dist_kind == B200HEAD_DIST_COSINE) ? sdtc::bwd_kernel<0> : sdtc::bwd_kernel<1>;
         B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sdtc::BWD_SMEM));
-        kern<<<B, sdtc::THREADS, sdtc::BWD_SMEM, st>>>(mx, my, x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx, dy);
+        kern<<<P, sdtc::THREADS, sdtc::BWD_SMEM, st>>>(mx, my, x, y, grad_out, N, M, d, bandwidth, cell, nx, ny, E, dx,
+                                                       dy, ix, iy);
 #endif
         b200::note_launches(1);
         B200_LAUNCH_OK("sdtw fused backward kernel");
@@ -549,12 +561,14 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
     }
     const int T = std::max(32, (N + 31) / 32 * 32);
     const size_t sh = 2 * (size_t)(T + 1) * sizeof(float2) + (size_t)M * sizeof(float);
-    dim3 gx((d + GD - 1) / GD, (N + GR - 1) / GR, B), gy((d + GD - 1) / GD, (M + GR - 1) / GR, B);
-#define SDTW_BWD(KIND)                                                                             \
-    do {                                                                                           \
-        dp_bwd_kernel<KIND><<<B, T, sh, st>>>(cell, grad_out, N, M, bandwidth, E, acoef, rsum, csum); \
-        grad_kernel<KIND><<<gx, 256, 0, st>>>(acoef, (long long)M, 1ll, N, M, d, y, x, nx, ny, rsum, dx); \
-        grad_kernel<KIND><<<gy, 256, 0, st>>>(acoef, 1ll, (long long)M, M, N, d, x, y, ny, nx, csum, dy); \
+    dim3 gx((d + GD - 1) / GD, (N + GR - 1) / GR, P), gy((d + GD - 1) / GD, (M + GR - 1) / GR, P);
+#define SDTW_BWD(KIND)                                                                                            \
+    do {                                                                                                          \
+        dp_bwd_kernel<KIND><<<P, T, sh, st>>>(cell, grad_out, N, M, bandwidth, E, acoef, rsum, csum);             \
+        grad_kernel<KIND><<<gx, 256, 0, st>>>(acoef, (long long)M, 1ll, N, M, d, y, x, nx, ny, rsum, dx, iy, ix,  \
+                                              accumulate);                                                        \
+        grad_kernel<KIND><<<gy, 256, 0, st>>>(acoef, 1ll, (long long)M, M, N, d, x, y, ny, nx, csum, dy, ix, iy,  \
+                                              accumulate);                                                        \
     } while (0)
     if (dist_kind == B200HEAD_DIST_COSINE) SDTW_BWD(B200HEAD_DIST_COSINE);
     else if (dist_kind == B200HEAD_DIST_NEGATIVE_DOT) SDTW_BWD(B200HEAD_DIST_NEGATIVE_DOT);
@@ -562,8 +576,55 @@ extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_o
 #undef SDTW_BWD
     b200::note_launches(3);
     B200_LAUNCH_OK("sdtw backward kernels");
-    (void)gamma;
     return 0;
+}
+
+int check_pairs(const char *who, int Bx, int By, const int *ix, const int *iy, int P) {
+    if (Bx <= 0 || By <= 0 || P <= 0) {
+        b200::set_error("%s: Bx, By and P must be positive (got %d %d %d)", who, Bx, By, P);
+        return B200HEAD_ERR_ARG;
+    }
+    if ((!ix && P != Bx) || (!iy && P != By)) {
+        b200::set_error("%s: a bank without an index list must hold exactly P = %d sequences", who, P);
+        return B200HEAD_ERR_ARG;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int sdtw_forward(const float *x, const float *y, int B, int N, int M, int d, float gamma,
+                            float bandwidth, int dist_kind, float *R, float *out, void *aux,
+                            size_t aux_bytes, void *stream) {
+    return forward_impl("sdtw_forward", x, B, y, B, nullptr, nullptr, B, N, M, d, gamma, bandwidth, dist_kind, R, out,
+                        aux, aux_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int sdtw_backward(const float *x, const float *y, const float *grad_out, int B, int N,
+                             int M, int d, float gamma, float bandwidth, int dist_kind,
+                             const void *aux, size_t aux_bytes, float *E, float *dx, float *dy,
+                             void *stream) {
+    return backward_impl("sdtw_backward", x, B, y, B, nullptr, nullptr, B, grad_out, N, M, d, gamma, bandwidth,
+                         dist_kind, aux, aux_bytes, E, dx, dy, (cudaStream_t)stream);
+}
+
+extern "C" int sdtw_forward_pairs(const float *x, int Bx, const float *y, int By, const int *ix, const int *iy,
+                                  int P, int N, int M, int d, float gamma, float bandwidth, int dist_kind,
+                                  float *R, float *out, void *aux, size_t aux_bytes, void *stream) {
+    int rc = check_pairs("sdtw_forward_pairs", Bx, By, ix, iy, P);
+    if (rc) return rc;
+    return forward_impl("sdtw_forward_pairs", x, Bx, y, By, ix, iy, P, N, M, d, gamma, bandwidth, dist_kind, R, out,
+                        aux, aux_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int sdtw_backward_pairs(const float *x, int Bx, const float *y, int By, const int *ix, const int *iy,
+                                   int P, const float *grad_out, int N, int M, int d, float gamma,
+                                   float bandwidth, int dist_kind, const void *aux, size_t aux_bytes, float *E,
+                                   float *dx, float *dy, void *stream) {
+    int rc = check_pairs("sdtw_backward_pairs", Bx, By, ix, iy, P);
+    if (rc) return rc;
+    return backward_impl("sdtw_backward_pairs", x, Bx, y, By, ix, iy, P, grad_out, N, M, d, gamma, bandwidth,
+                         dist_kind, aux, aux_bytes, E, dx, dy, (cudaStream_t)stream);
 }
 
 // ----------------------------------------------------------------------------

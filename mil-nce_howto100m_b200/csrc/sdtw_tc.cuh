@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(THREADS, 2)
 fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_y, int N, int M,
            int d, float gamma, float bandwidth, float *__restrict__ Rout, float *__restrict__ out,
            float4 *__restrict__ cell, float *__restrict__ nx_out, float *__restrict__ ny_out,
-           int *__restrict__ overflow) {
+           int *__restrict__ overflow, const int *__restrict__ ix, const int *__restrict__ iy) {
     extern __shared__ uint8_t smem_raw[];
     // 1 KB alignment as pointer arithmetic ON the shared array: a round trip through an integer makes the
     // compiler treat every later access as generic (LD/ST instead of LDS/STS), which doubled the time
@@ -169,6 +169,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nchunks = (d + KC - 1) / KC;
     const int ngroups = (nchunks + FLUSH - 1) / FLUSH;
+    // pair b compares sequence bx of the x bank with sequence by of the y bank (identity without index lists)
+    const int bx = ix ? ix[b] : b, by = iy ? iy[b] : b;
     SDTC_STAMP(0, 0);
 
     if (warp == 0 && lane == 0) {
@@ -200,8 +202,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             if (tc::elect_one()) {
                 uint8_t *st = smem + stage * STAGE_BYTES;
                 tc::mbar_expect_tx(&tl.full[stage], 2 * OPER_BYTES);
-                tma_load_3d(st, &map_x, &tl.full[stage], c * KC, 0, b);
-                tma_load_3d(st + 2 * OPER_BYTES, &map_y, &tl.full[stage], c * KC, 0, b);
+                tma_load_3d(st, &map_x, &tl.full[stage], c * KC, 0, bx);
+                tma_load_3d(st + 2 * OPER_BYTES, &map_y, &tl.full[stage], c * KC, 0, by);
             }
             __syncwarp();
             if (++stage == STAGES) {
@@ -545,7 +547,8 @@ struct BwdTail {
     float rsum[T], csum[T];
     unsigned long long mb[2 * T];
 };
-constexpr int BWD_SMEM = W_BYTES + 2 * A_BYTES + (int)sizeof(BwdTail) + 1024;
+constexpr int STG_BYTES = 4 * 32 * 20 * 4;         // 10 KB: one 32 x (16 + 4) float staging tile per drain warp
+constexpr int BWD_SMEM = W_BYTES + 2 * A_BYTES + STG_BYTES + (int)sizeof(BwdTail) + 1024;
 
 __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -574,16 +577,21 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
            const float *__restrict__ x, const float *__restrict__ y, const float *__restrict__ grad_out, int N,
            int M, int d, float bandwidth, const float4 *__restrict__ cell, const float *__restrict__ nx_in,
            const float *__restrict__ ny_in, float *__restrict__ Eout, float *__restrict__ dx,
-           float *__restrict__ dy) {
+           float *__restrict__ dy, const int *__restrict__ ix, const int *__restrict__ iy) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t *a_hi = smem + W_BYTES, *a_lo = a_hi + A_BYTES;
     float *Et = reinterpret_cast<float *>(a_hi);          // raw E, [j][i], until the coefficient pass
-    BwdTail &tl = *reinterpret_cast<BwdTail *>(smem + W_BYTES + 2 * A_BYTES);
+    float *stage = reinterpret_cast<float *>(smem + W_BYTES + 2 * A_BYTES);
+    BwdTail &tl = *reinterpret_cast<BwdTail *>(smem + W_BYTES + 2 * A_BYTES + STG_BYTES);
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nchunks = (d + KC - 1) / KC;
     const int steps = N + M - 1;
     const uint32_t wbytes = (uint32_t)(N * M * 16);
+    // pair b = (sequence bx of the x bank, sequence by of the y bank); with index lists several pairs may share
+    // a sequence, so its gradient is accumulated with atomic adds (the host zeroes dx / dy first)
+    const int bx = ix ? ix[b] : b, by = iy ? iy[b] : b;
+    const bool accumulate = (ix != nullptr) || (iy != nullptr);
     SDTC_STAMP(8, 0);
 #ifdef SDTW_PROFILE
     if (blockIdx.x == 0 && tid == 0) fused::g_prof[21] = 0;
@@ -800,8 +808,8 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             const int c = t < nitems1 ? t : t - nitems1;
             if (tc::elect_one()) {
                 const CUtensorMap *mp = t < nitems1 ? &map_x : &map_y;
-                tma_prefetch_l2_3d(mp, c * BFC, 0, b);
-                if (c * BFC + KC < d) tma_prefetch_l2_3d(mp, c * BFC + KC, 0, b);
+                tma_prefetch_l2_3d(mp, c * BFC, 0, t < nitems1 ? bx : by);
+                if (c * BFC + KC < d) tma_prefetch_l2_3d(mp, c * BFC + KC, 0, t < nitems1 ? bx : by);
             }
             __syncwarp();
         };
@@ -825,8 +833,9 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                 // keeps stale data, which only reaches output columns that are never stored
                 const bool two = c * BFC + KC < d;
                 tc::mbar_expect_tx(&tl.full[stage], two ? 2 * OPER_BYTES : OPER_BYTES);
-                tma_load_3d(st, mp, &tl.full[stage], c * BFC, 0, b);
-                if (two) tma_load_3d(st + OPER_BYTES, mp, &tl.full[stage], c * BFC + KC, 0, b);
+                const int bb = t < nitems1 ? by : bx;          // pass 0 streams y, pass 1 streams x
+                tma_load_3d(st, mp, &tl.full[stage], c * BFC, 0, bb);
+                if (two) tma_load_3d(st + OPER_BYTES, mp, &tl.full[stage], c * BFC + KC, 0, bb);
                 SDTC_ISTAMP(22, t == 5);
             }
             __syncwarp();
@@ -928,34 +937,41 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     } else {
         // drain warps.  TMEM lane 32 q + l holds, for tile row m = 16 q + (l & 15), the A~_hi products (l < 16)
         // or the A~_lo products (l >= 16); columns 0..63 are . chunk_hi, 64..127 . chunk_lo.  Lane l and lane
-        // l ^ 16 swap partial sums by shuffle: the hi lane finishes features 0..31 of the item, the lo lane
-        // features 32..63 (own-vector term from global memory - the TMA warp put the tile into L2 - and a
-        // full 128-byte row segment stored per lane).
+        // l ^ 16 swap partial sums by shuffle: the hi lane ends up with features 0..31 of the item for its
+        // row, the lo lane with features 32..63.
+        // Global memory is then accessed through a per-warp staging tile, FOUR lanes per 64-byte row piece:
+        // with one lane per row a warp instruction touched 32 different lines (rows are d floats apart) and
+        // the load/store unit, not DRAM, bounded the kernel (measured: 37 k cycles for the loads and as
+        // much for the stores, per pair).
         const int q = warp & 3;
         const int m = q * 16 + (lane & 15);
         const bool hi_lane = lane < 16;
-        const int myh = hi_lane ? 0 : 1;
+        float *stg = stage + (warp - 6) * (32 * 20);           // [32 rows][16 floats + 4 pad]
+        const int cidx = lane & 3;                             // float4 column within a 16-feature piece
         for (int t = 0; t < nitems; ++t) {
             if (t == nitems1) boundary();
             const bool px = t < nitems1;
             const int c = px ? t : t - nitems1;
             const uint32_t buf = t & 1;
             const int rows = px ? N : M;
-            const float own = px ? tl.ownx[m] : tl.owny[m];
-            const int f0 = c * BFC + myh * 32;                 // first feature this lane stores
-            const float *self = (px ? x + (size_t)b * N * d : y + (size_t)b * M * d) + (size_t)m * d + f0;
-            float *dst = (px ? dx + (size_t)b * N * d : dy + (size_t)b * M * d) + (size_t)m * d + f0;
-            const bool live = m < rows;
-            // the own-vector operand of the whole item first (L2 hits, ~1 k cycles under load): issued before
-            // the wait for the MMAs so that the latency runs under the wait and the TMEM loads
+            const float *selfb = px ? x + (size_t)bx * N * d : y + (size_t)by * M * d;
+            float *dstb = px ? dx + (size_t)bx * N * d : dy + (size_t)by * M * d;
+            const float *ownv = px ? tl.ownx : tl.owny;
+            // staging row R = rr * 8 + lane / 4 belongs to lane R of this warp: tile row 16 q + (R & 15), half R >> 4
+            // the own-vector operand of the whole item first (mostly L2 hits): issued before the wait for the MMAs
             float4 sv[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                sv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-#ifndef SDTC_EXP_NO_GLOBAL
-                if (KIND == 0 && live && f0 + 4 * u < d) sv[u] = __ldg(reinterpret_cast<const float4 *>(self) + u);
+            for (int g = 0; g < 2; ++g)
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int R = rr * 8 + (lane >> 2);
+                    const int mr = q * 16 + (R & 15);
+                    const int f = c * BFC + (R >> 4) * 32 + g * 16 + cidx * 4;
+                    sv[g * 4 + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+#if !defined(SDTC_EXP_NO_GLOBAL) && !defined(SDTC_EXP_NO_LOADS)
+                    if (KIND == 0 && mr < rows && f < d) sv[g * 4 + rr] = __ldg(reinterpret_cast<const float4 *>(selfb + (size_t)mr * d + f));
 #endif
-            }
+                }
             tc::mbar_wait(&tl.tfull[buf], (t >> 1) & 1);
             SDTC_ISTAMP(27, t == 5 && tid == 192);
             tc::tcgen05_fence_after();
@@ -965,19 +981,12 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                 float p0[16], p1[16];              // this row's partial sums: features 16 g .. (half 0), 32 + 16 g .. (half 1)
                 {
                     float w[16];
-#ifdef SDTC_EXP_NO_TMEM
-#pragma unroll
-                    for (int u = 0; u < 16; ++u) { w[u] = (float)u; p0[u] = (float)(u + t); p1[u] = (float)(u - t); }
-#else
                     tmem_ld16(ta + 64 + g * 16, w);            // . chunk_lo (small terms)
                     tmem_ld16(ta + g * 16, p0);
-#endif
 #pragma unroll
                     for (int u = 0; u < 16; ++u) p0[u] += w[u];
-#ifndef SDTC_EXP_NO_TMEM
                     tmem_ld16(ta + 96 + g * 16, w);
                     tmem_ld16(ta + 32 + g * 16, p1);
-#endif
 #pragma unroll
                     for (int u = 0; u < 16; ++u) p1[u] += w[u];
                 }
@@ -986,31 +995,39 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                     tc::mbar_arrive(&tl.tempty[buf]);
                     SDTC_ISTAMP(28, t == 5 && tid == 192);
                 }
-                float o[16];
 #pragma unroll
-                for (int u = 0; u < 16; ++u) {
-                    const float recv = __shfl_xor_sync(0xffffffffu, hi_lane ? p1[u] : p0[u], 16);
-                    o[u] = (hi_lane ? p0[u] : p1[u]) + recv;
+                for (int u = 0; u < 16; u += 4) {
+                    float o[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float recv = __shfl_xor_sync(0xffffffffu, hi_lane ? p1[u + e] : p0[u + e], 16);
+                        o[e] = (hi_lane ? p0[u + e] : p1[u + e]) + recv;
+                    }
+                    *reinterpret_cast<float4 *>(stg + lane * 20 + u) = make_float4(o[0], o[1], o[2], o[3]);
                 }
-                if (live) {
+                __syncwarp();
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        if (f0 + g * 16 + 4 * u < d) {         // d % 4 == 0: a float4 is all in or all out
-                            float4 r4 = make_float4(o[4 * u], o[4 * u + 1], o[4 * u + 2], o[4 * u + 3]);
-                            if (KIND == 0) {
-                                const float4 s4 = sv[g * 4 + u];
-                                r4.x = fmaf(own, s4.x, r4.x); r4.y = fmaf(own, s4.y, r4.y);
-                                r4.z = fmaf(own, s4.z, r4.z); r4.w = fmaf(own, s4.w, r4.w);
-                            }
-#ifdef SDTC_EXP_NO_GLOBAL
-                            if (r4.x == 12345.678f)
+                for (int rr = 0; rr < 4; ++rr) {
+                    const int R = rr * 8 + (lane >> 2);
+                    const int mr = q * 16 + (R & 15);
+                    const int f = c * BFC + (R >> 4) * 32 + g * 16 + cidx * 4;
+                    float4 r4 = *reinterpret_cast<const float4 *>(stg + R * 20 + cidx * 4);
+                    if (KIND == 0) {
+                        const float own = ownv[mr];
+                        const float4 s4 = sv[g * 4 + rr];
+                        r4.x = fmaf(own, s4.x, r4.x); r4.y = fmaf(own, s4.y, r4.y);
+                        r4.z = fmaf(own, s4.z, r4.z); r4.w = fmaf(own, s4.w, r4.w);
+                    }
+                    if (mr < rows && f < d) {      // d % 4 == 0: a float4 is all in or all out
+#if defined(SDTC_EXP_NO_GLOBAL) || defined(SDTC_EXP_NO_STORES)
+                        if (r4.x == 12345.678f)
 #endif
-                            // streaming store: the gradients are not read again here, and x / y should stay in
-                            // L2 for the second pass (own-vector term, then the TMA stream)
-                            __stcs(reinterpret_cast<float4 *>(dst + g * 16) + u, r4);
-                        }
+                        // streaming store: the gradients are not read again here, x / y should stay in L2
+                        if (accumulate) atomicAdd(reinterpret_cast<float4 *>(dstb + (size_t)mr * d + f), r4);
+                        else __stcs(reinterpret_cast<float4 *>(dstb + (size_t)mr * d + f), r4);
                     }
                 }
+                __syncwarp();                      // the staging tile is free again
             }
             SDTC_ISTAMP(29, t == 5 && tid == 192);
         }

@@ -86,6 +86,59 @@ class _SoftDTWFunction(torch.autograd.Function):
         return dx, dy, None, None, None
 
 
+def _iptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+class _SoftDTWPairsFunction(torch.autograd.Function):
+    """soft-DTW of index pairs (sdtw_forward_pairs / sdtw_backward_pairs of the C ABI): pair p compares
+    X[ix[p]] with Y[iy[p]].  The gradient of a sequence is the sum over the pairs it takes part in."""
+
+    @staticmethod
+    def forward(ctx, X, Y, ix, iy, gamma, bandwidth, dist_kind):
+        lib = _lib.load()
+        x = X.detach().contiguous()
+        y = Y.detach().contiguous()
+        Bx, N, d = x.shape
+        By, M, _ = y.shape
+        ix = None if ix is None else ix.to(device=x.device, dtype=torch.int32).contiguous()
+        iy = None if iy is None else iy.to(device=x.device, dtype=torch.int32).contiguous()
+        P = ix.numel() if ix is not None else (iy.numel() if iy is not None else Bx)
+        dev = x.device
+        aux_bytes = lib.sdtw_aux_bytes(P, N, M, d)
+        aux = torch.empty(aux_bytes, dtype=torch.uint8, device=dev)
+        out = torch.empty(P, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.sdtw_forward_pairs(_ptr(x), Bx, _ptr(y), By, _iptr(ix), _iptr(iy), P, N, M, d, float(gamma),
+                                        float(bandwidth), int(dist_kind), _ptr(None), _ptr(out), _ptr(aux), aux_bytes,
+                                        _lib.stream_ptr(dev))
+        _lib.check(rc, "sdtw_forward_pairs")
+        ctx.save_for_backward(x, y)
+        ctx.idx = (ix, iy, P)
+        ctx.aux = aux
+        ctx.cfg = (float(gamma), float(bandwidth), int(dist_kind))
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        lib = _lib.load()
+        x, y = ctx.saved_tensors
+        ix, iy, P = ctx.idx
+        gamma, bandwidth, dist_kind = ctx.cfg
+        Bx, N, d = x.shape
+        By, M, _ = y.shape
+        g = grad_output.detach().to(torch.float32).contiguous()
+        dx = torch.empty_like(x)
+        dy = torch.empty_like(y)
+        dev = x.device
+        with torch.cuda.device(dev):
+            rc = lib.sdtw_backward_pairs(_ptr(x), Bx, _ptr(y), By, _iptr(ix), _iptr(iy), P, _ptr(g), N, M, d, gamma,
+                                         bandwidth, dist_kind, _ptr(ctx.aux), ctx.aux.numel(), _ptr(None), _ptr(dx),
+                                         _ptr(dy), _lib.stream_ptr(dev))
+        _lib.check(rc, "sdtw_backward_pairs")
+        return dx, dy, None, None, None, None, None
+
+
 class SoftDTW(torch.nn.Module):
     """The soft-DTW module of the reference, backed by sm_100a kernels."""
 
@@ -128,9 +181,32 @@ class SoftDTW(torch.nn.Module):
         if self.normalize:
             if X.shape[1] != Y.shape[1]:
                 raise RuntimeError("normalize=True needs equal sequence lengths (torch.cat, :378)")
-            x = torch.cat([X, X, Y])
-            y = torch.cat([Y, X, Y])
-            out = _SoftDTWFunction.apply(x, y, self.gamma, self.bandwidth, kind)
-            out_xy, out_xx, out_yy = torch.split(out, X.shape[0])
+            # The reference stacks cat([X, X, Y]) against cat([Y, X, Y]) (soft_dtw_cuda.py:378-379): three
+            # batches of pairs.  Here each batch reads its operands where they are - no stacked copies.
+            out_xy = _SoftDTWFunction.apply(X, Y, self.gamma, self.bandwidth, kind)
+            out_xx = _SoftDTWFunction.apply(X, X, self.gamma, self.bandwidth, kind)
+            out_yy = _SoftDTWFunction.apply(Y, Y, self.gamma, self.bandwidth, kind)
             return out_xy - 1 / 2 * (out_xx + out_yy)
         return _SoftDTWFunction.apply(X, Y, self.gamma, self.bandwidth, kind)
+
+    def forward_pairs(self, X, Y, ix=None, iy=None):
+        """soft-DTW of the pairs (X[ix[p]], Y[iy[p]]) -> (P,).  Not in the reference API: it replaces the
+        expand(...).reshape(...) / repeat(...) operand copies its composite losses make before calling
+        forward (loss.py:29, 101-105); normalize is not applied."""
+        self._check_pairs(X, Y)
+        kind = _lib.DIST_KINDS[self.dist_func]
+        return _SoftDTWPairsFunction.apply(X, Y, ix, iy, self.gamma, self.bandwidth, kind)
+
+    def _check_pairs(self, x, y):
+        if x.dim() != 3 or y.dim() != 3:
+            raise ValueError("X and Y must be (Bx, N, d) and (By, M, d)")
+        if x.shape[2] != y.shape[2]:
+            raise ValueError("feature dimensions differ")
+        if not self.use_cuda:
+            raise RuntimeError("SoftDTW(use_cuda=False): this package has no CPU path")
+        if x.shape[1] > 1024 or y.shape[1] > 1024:
+            raise RuntimeError("SoftDTW: sequence length > 1024 is not supported")
+        if not (x.is_cuda and y.is_cuda):
+            raise RuntimeError("SoftDTW runs on CUDA tensors only")
+        if x.dtype != torch.float32 or y.dtype != torch.float32:
+            raise TypeError("SoftDTW supports float32 inputs")

@@ -121,11 +121,65 @@ def golden_sdtw(ref_sdtw):
         print(f"sdtw_{name}: {len(rec)} arrays")
 
 
+def golden_composite(ref_loss, ref_sdtw):
+    """The composite soft-DTW losses of reference loss.py:20-134 (CDTW, SDTW_CIDM, SDTW_3), executed with
+    the one deviation the docstring above names: every ``SoftDTW(use_cuda=True, ...)`` they construct is
+    built with ``use_cuda=False`` (numba-CPU path); their own code is not touched."""
+    class Args:
+        rank = 1
+
+    real = ref_sdtw.SoftDTW
+
+    def cpu_sdtw(use_cuda, *a, **k):
+        return real(False, *a, **k)
+
+    ref_loss.SoftDTW = cpu_sdtw
+    try:
+        rec = {}
+        g = torch.Generator().manual_seed(31)
+        # CDTW: batch of 8 (the reference hard-codes repeat(8, ...), :29), frames 6 / words 5, d = 16
+        v32 = torch.randn(8, 6, 16, generator=g)
+        t32 = torch.randn(8, 5, 16, generator=g)
+        v = v32.double().requires_grad_(True)
+        t = t32.double().requires_grad_(True)
+        out = ref_loss.CDTW(Args())(v, t)
+        out.sum().backward()
+        rec.update(cdtw_video=v32.numpy(), cdtw_text=t32.numpy(), cdtw_out=out.detach().numpy(),
+                   cdtw_dvideo=v.grad.numpy(), cdtw_dtext=t.grad.numpy())
+        # SDTW_3: b = 4 sequences of 6 frames, d = 16 (all 16 pairs per term)
+        v32 = torch.randn(4, 6, 16, generator=g) * 0.5
+        t32 = torch.randn(4, 6, 16, generator=g) * 0.5
+        v = v32.double().requires_grad_(True)
+        t = t32.double().requires_grad_(True)
+        l1, l2, l3 = ref_loss.SDTW_3(Args())(v, t)
+        (l1 + 2.0 * l2 + 3.0 * l3).backward()
+        rec.update(s3_video=v32.numpy(), s3_text=t32.numpy(), s3_losses=np.array([l1.item(), l2.item(), l3.item()]),
+                   s3_dvideo=v.grad.numpy(), s3_dtext=t.grad.numpy())
+        # SDTW_CIDM: b = 3, n = m = 6, start times spread so that both branches of `y` occur
+        v32 = torch.randn(3, 6, 16, generator=g)
+        t32 = torch.randn(3, 6, 16, generator=g)
+        start = torch.cumsum(torch.rand(3, 6, generator=g) * 8.0, dim=1).double()
+        end = start + 1.0
+        v = v32.double().requires_grad_(True)
+        t = t32.double().requires_grad_(True)
+        out = ref_loss.SDTW_CIDM(Args())(v, t, start, end)
+        out.backward()
+        rec.update(cidm_video=v32.numpy(), cidm_text=t32.numpy(), cidm_start=start.numpy(), cidm_end=end.numpy(),
+                   cidm_out=np.float64(out.item()), cidm_dvideo=v.grad.numpy(), cidm_dtext=t.grad.numpy())
+        np.savez_compressed(os.path.join(OUT, "composite_losses.npz"), **rec)
+        print(f"composite_losses: {len(rec)} arrays; CDTW {rec['cdtw_out']}, SDTW_3 {rec['s3_losses']}, "
+              f"SDTW_CIDM {rec['cidm_out']}")
+    finally:
+        ref_loss.SoftDTW = real
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref_loss, ref_sdtw = _import_reference()
-    golden_milnce(ref_loss)
-    golden_sdtw(ref_sdtw)
+    if "--composite-only" not in sys.argv:
+        golden_milnce(ref_loss)
+        golden_sdtw(ref_sdtw)
+    golden_composite(ref_loss, ref_sdtw)
 
 
 if __name__ == "__main__":
