@@ -939,15 +939,17 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
         // or the A~_lo products (l >= 16); columns 0..63 are . chunk_hi, 64..127 . chunk_lo.  Lane l and lane
         // l ^ 16 swap partial sums by shuffle: the hi lane ends up with features 0..31 of the item for its
         // row, the lo lane with features 32..63.
-        // Global memory is then accessed through a per-warp staging tile, FOUR lanes per 64-byte row piece:
-        // with one lane per row a warp instruction touched 32 different lines (rows are d floats apart) and
-        // the load/store unit, not DRAM, bounded the kernel (measured: 37 k cycles for the loads and as
-        // much for the stores, per pair).
+        // In step g of an item the hi lane ends up with features 32 g .. 32 g + 15 of its row, the lo lane with
+        // 32 g + 16 .. 32 g + 31: together one 128-byte piece of the row.
+        // Global memory is accessed through a per-warp staging tile, EIGHT lanes per 128-byte row piece, so a
+        // warp instruction touches 4 full lines.  With one lane per row it touched 32 different lines (rows
+        // are d floats apart) and the load/store unit, not DRAM, bounded the kernel (measured: 37 k cycles
+        // for the loads and as much for the stores, per pair).
         const int q = warp & 3;
-        const int m = q * 16 + (lane & 15);
         const bool hi_lane = lane < 16;
-        float *stg = stage + (warp - 6) * (32 * 20);           // [32 rows][16 floats + 4 pad]
-        const int cidx = lane & 3;                             // float4 column within a 16-feature piece
+        float *stg = stage + (warp - 6) * (32 * 20);           // [32 lanes][16 floats + 4 pad]
+        const int c8 = lane & 7;                               // float4 column within a 32-feature piece
+        const int srow_off = (c8 >= 4 ? 16 : 0);               // second half of the piece: the lo lane's staging row
         for (int t = 0; t < nitems; ++t) {
             if (t == nitems1) boundary();
             const bool px = t < nitems1;
@@ -957,16 +959,14 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             const float *selfb = px ? x + (size_t)bx * N * d : y + (size_t)by * M * d;
             float *dstb = px ? dx + (size_t)bx * N * d : dy + (size_t)by * M * d;
             const float *ownv = px ? tl.ownx : tl.owny;
-            // staging row R = rr * 8 + lane / 4 belongs to lane R of this warp: tile row 16 q + (R & 15), half R >> 4
             // the own-vector operand of the whole item first (mostly L2 hits): issued before the wait for the MMAs
             float4 sv[8];
 #pragma unroll
             for (int g = 0; g < 2; ++g)
 #pragma unroll
                 for (int rr = 0; rr < 4; ++rr) {
-                    const int R = rr * 8 + (lane >> 2);
-                    const int mr = q * 16 + (R & 15);
-                    const int f = c * BFC + (R >> 4) * 32 + g * 16 + cidx * 4;
+                    const int mr = q * 16 + rr * 4 + (lane >> 3);
+                    const int f = c * BFC + g * 32 + c8 * 4;
                     sv[g * 4 + rr] = make_float4(0.f, 0.f, 0.f, 0.f);
 #if !defined(SDTC_EXP_NO_GLOBAL) && !defined(SDTC_EXP_NO_LOADS)
                     if (KIND == 0 && mr < rows && f < d) sv[g * 4 + rr] = __ldg(reinterpret_cast<const float4 *>(selfb + (size_t)mr * d + f));
@@ -978,15 +978,15 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
             const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 128;
 #pragma unroll
             for (int g = 0; g < 2; ++g) {          // 16 features of each half per step
-                float p0[16], p1[16];              // this row's partial sums: features 16 g .. (half 0), 32 + 16 g .. (half 1)
+                float p0[16], p1[16];              // this row's partial sums: features 32 g .. + 15 and 32 g + 16 .. + 31
                 {
                     float w[16];
-                    tmem_ld16(ta + 64 + g * 16, w);            // . chunk_lo (small terms)
-                    tmem_ld16(ta + g * 16, p0);
+                    tmem_ld16(ta + 64 + g * 32, w);            // . chunk_lo (small terms)
+                    tmem_ld16(ta + g * 32, p0);
 #pragma unroll
                     for (int u = 0; u < 16; ++u) p0[u] += w[u];
-                    tmem_ld16(ta + 96 + g * 16, w);
-                    tmem_ld16(ta + 32 + g * 16, p1);
+                    tmem_ld16(ta + 64 + g * 32 + 16, w);
+                    tmem_ld16(ta + g * 32 + 16, p1);
 #pragma unroll
                     for (int u = 0; u < 16; ++u) p1[u] += w[u];
                 }
@@ -1008,10 +1008,10 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
                 __syncwarp();
 #pragma unroll
                 for (int rr = 0; rr < 4; ++rr) {
-                    const int R = rr * 8 + (lane >> 2);
-                    const int mr = q * 16 + (R & 15);
-                    const int f = c * BFC + (R >> 4) * 32 + g * 16 + cidx * 4;
-                    float4 r4 = *reinterpret_cast<const float4 *>(stg + R * 20 + cidx * 4);
+                    const int tr = rr * 4 + (lane >> 3);               // tile row within this warp's 16
+                    const int mr = q * 16 + tr;
+                    const int f = c * BFC + g * 32 + c8 * 4;
+                    float4 r4 = *reinterpret_cast<const float4 *>(stg + (tr + srow_off) * 20 + (c8 & 3) * 4);
                     if (KIND == 0) {
                         const float own = ownv[mr];
                         const float4 s4 = sv[g * 4 + rr];
