@@ -168,7 +168,10 @@ class _GatheredMILNCERows(torch.autograd.Function):
         i0, b, backend, vdt, tdt, group, bk_local, marks, pdt = ctx.meta
         _mark(marks, "backward_start", V.device)
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
-        pdt = pdt if pdt is not None else torch.float32
+        # default: partials in the embeddings' own 16-bit dtype - the result is rounded to that dtype anyway, and
+        # a float32 payload (67 MB at B=8192) made the reduce-scatter the longest phase of the step
+        # (profiles/r2_multi_timeline_*.txt); float32 on request (partial_dtype=torch.float32)
+        pdt = pdt if pdt is not None else (torch.bfloat16 if tdt == torch.bfloat16 else torch.float32)
         # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
         _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt)
         _mark(marks, "gradient_tiles+dtext_partial", V.device)
@@ -195,8 +198,8 @@ class GatheredMILNCELoss(torch.nn.Module):
         """scheme: "rows" (each rank computes only its rows of S, reduce-scatter of the text
         gradient; bf16 embeddings), "rowcol" (row block + column block per rank, no gradient
         collective - the reference's communication pattern), or "auto" (rows when available).
-        partial_dtype: dtype of the rows scheme's text-gradient partials on the wire (default:
-        float32; torch.bfloat16 halves the reduce-scatter).
+        partial_dtype: dtype of the rows scheme's text-gradient partials on the wire (default: the
+        embeddings' dtype, i.e. bfloat16; torch.float32 doubles the reduce-scatter payload).
         _backend: private test seam (the CPU tests drive the orchestration with a stand-in)."""
         super().__init__()
         if scheme not in ("auto", "rows", "rowcol"):
