@@ -116,6 +116,25 @@ int milnce_forward_shard(const void *video, const void *text, int B, int K, int 
  * similarity matrix is reduced on every rank, loss.py:16-18.) */
 int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom, float *loss,
                          void *stream);
+/* Rows-only sharding WITHOUT an embedding collective.  Every rank publishes its bfloat16 shard in a buffer
+ * that its peers can read directly (peer-mapped memory, e.g. torch symmetric memory: slot pointers of all
+ * ranks are exchanged once at set-up), and stages the fp16 operands of all W ranks straight from the
+ * peers' buffers with plain loads over NVLink - the gather of utils.py:11-17 and the staging pass become one
+ * kernel.  Per step and rank:
+ *   milnce_peer_publish      copies the local shard into this rank's slot (milnce_peer_slot_bytes), leaves
+ *                            |video|max, |text|max in the slot header and nom[0, b) of the local samples;
+ *   <the caller's cross-rank barrier: every slot is complete>
+ *   milnce_forward_shard_peers  reads all slots (slots[r] = rank r's slot as mapped into THIS process),
+ *                            then as milnce_forward_shard: row_lse[i0, i0+n), col_part[0, B).
+ * Backward: milnce_backward_shard with reuse_forward_ws = 1 (it reads only the workspace).  The caller must
+ * not let a rank overwrite its slot while a peer may still be reading it (two slots used alternately and the
+ * per-step barrier are enough).  Needs b = B / W a multiple of 64, D a multiple of 8, W <= 16. */
+size_t milnce_peer_slot_bytes(int b, int K, int D);
+int milnce_peer_publish(const void *video_local, const void *text_local, int b, int K, int D, void *slot,
+                        float *nom_own, void *stream);
+int milnce_forward_shard_peers(const void *const *host_slots, int W, int B, int K, int D, int i0, int n,
+                               float *row_lse, float *col_part, void *workspace, size_t workspace_bytes,
+                               void *stream);
 int milnce_backward_shard(const void *video, const void *text, const float *den, const float *nom,
                           const float *grad_loss, void *dvideo, int dvideo_dtype, void *dtext_partial,
                           int dtext_dtype, int parts, int B, int K, int D, int dtype, int i0, int n,

@@ -95,6 +95,12 @@ def _declare(lib):
                                     vp, sz, vp]
     lib.milnce_forward_shard.restype = i32
     lib.milnce_forward_shard.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, fp, fp, fp, vp, sz, vp]
+    lib.milnce_peer_slot_bytes.restype = sz
+    lib.milnce_peer_slot_bytes.argtypes = [i32, i32, i32]
+    lib.milnce_peer_publish.restype = i32
+    lib.milnce_peer_publish.argtypes = [vp, vp, i32, i32, i32, vp, fp, vp]
+    lib.milnce_forward_shard_peers.restype = i32
+    lib.milnce_forward_shard_peers.argtypes = [c.POINTER(c.c_void_p), i32, i32, i32, i32, i32, i32, fp, fp, vp, sz, vp]
     lib.milnce_shard_combine.restype = i32
     lib.milnce_shard_combine.argtypes = [fp, i32, i32, fp, fp, fp, vp]
     lib.milnce_backward_shard.restype = i32

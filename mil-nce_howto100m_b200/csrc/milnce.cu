@@ -401,6 +401,141 @@ prep_bf16_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *_
 }
 
 // ----------------------------------------------------------------------------
+// multi-GPU without an embedding collective: every rank PUBLISHES its bf16 shard in a buffer that its
+// peers can read (peer-mapped / symmetric memory), and stages the fp16 operands of ALL ranks straight
+// from the peers' buffers (plain 16-byte loads over NVLink; no TMA touches another GPU's memory).
+// Slot layout (milnce_peer_slot_bytes): 256-byte header {|video|max bits, |text|max bits} | video (b, D) |
+// text (b*K, D), bfloat16.
+// ----------------------------------------------------------------------------
+constexpr int PEER_MAX = 16;
+constexpr size_t PEER_HEADER = 256;
+struct PeerSlots {
+    const uint8_t *slot[PEER_MAX];
+};
+
+// one warp per local sample i: copies video[i] and its K candidates into the slot, accumulates the local
+// |x|max of both tensors into the slot header (atomicMax on float bits; the header is zeroed by the host
+// before the launch) and produces nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs (loss.py:13-15).
+__global__ void __launch_bounds__(256, 8)
+peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *__restrict__ text, int b, int K,
+                    int D, uint8_t *__restrict__ slot, float *__restrict__ nom_own) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    unsigned int *hdr = reinterpret_cast<unsigned int *>(slot);
+    uint4 *sv = reinterpret_cast<uint4 *>(slot + PEER_HEADER);
+    uint4 *stx = sv + (size_t)b * D / 8;
+    float mv = 0.f, mt = 0.f;
+    auto amax8 = [](float m, const float (&f)[8]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float a = fabsf(f[j]);
+            if (a == a && a <= 3.0e38f) m = fmaxf(m, a);
+        }
+        return m;
+    };
+    auto unpack8 = [](const uint4 &q, float (&f)[8]) {
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&q);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 v = __bfloat1622float2(h[j]);
+            f[2 * j] = v.x;
+            f[2 * j + 1] = v.y;
+        }
+    };
+    const int dv = D / 8;
+    for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < b; i += gridDim.x * wpb) {
+        const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
+        float pm = -INFINITY, ps = 0.f;
+        for (int k = 0; k < K; ++k) {
+            const uint4 *trow = reinterpret_cast<const uint4 *>(text + ((size_t)i * K + k) * D);
+            float acc = 0.f;
+            for (int c = lane; c < dv; c += 32) {
+                const uint4 qv = __ldg(vrow + c), qt = __ldg(trow + c);
+                float fv[8], ft[8];
+                unpack8(qv, fv);
+                unpack8(qt, ft);
+                if (k == 0) {
+                    mv = amax8(mv, fv);
+                    sv[(size_t)i * dv + c] = qv;
+                }
+                mt = amax8(mt, ft);
+                stx[((size_t)i * K + k) * dv + c] = qt;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc = fmaf(fv[j], ft[j], acc);
+            }
+            acc = warp_sum(acc);
+            if (acc > pm) {
+                ps = ps * expf(pm - acc) + 1.f;
+                pm = acc;
+            } else {
+                ps += expf(acc - pm);
+            }
+        }
+        if (lane == 0) nom_own[i] = pm + logf(ps);
+    }
+    mv = warp_max(mv);
+    mt = warp_max(mt);
+    if (lane == 0) {
+        if (mv > 0.f) atomicMax(&hdr[0], __float_as_uint(mv));
+        if (mt > 0.f) atomicMax(&hdr[1], __float_as_uint(mt));
+    }
+}
+
+// bf16 shards of all W ranks -> scaled fp16 K-major operands in the local workspace.  The power-of-two
+// scales come from the maximum over the W slot headers; block 0 publishes them for the later kernels.
+// D % 8 == 0, so the staged rows are unpadded and both tensors are flat arrays: a grid-stride loop over
+// 16-byte granules, eight independent loads in flight per thread, 512 contiguous bytes per warp
+// instruction.  (A 64 x 64-tile version with two loads per thread read the peers at 95 GB/s.)
+__global__ void __launch_bounds__(256)
+stage_peers_kernel(PeerSlots ps, int W, int b, int K, int D, __half *__restrict__ vk, __half *__restrict__ tk,
+                   Scalars *scal) {
+    unsigned int av = 0, at = 0;
+    for (int r = 0; r < W; ++r) {
+        const unsigned int *h = reinterpret_cast<const unsigned int *>(ps.slot[r]);
+        av = max(av, __ldcg(h));          // positive floats compare like their bit patterns
+        at = max(at, __ldcg(h + 1));
+    }
+    const float s_v = pow2_scale(av), s_t = pow2_scale(at);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        scal->absmax_bits[0] = av;
+        scal->absmax_bits[1] = at;
+        scal->s_video = s_v;
+        scal->s_text = s_t;
+        scal->inv_ss = (1.f / s_v) * (1.f / s_t);
+    }
+    const size_t gv = (size_t)b * D / 8, gt = gv * K;      // granules (8 elements) per shard: video, text
+    const size_t per = gv + gt, total = per * W;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    auto convert = [&](size_t g, const uint4 &q) {
+        const int r = (int)(g / per);
+        const size_t o = g - (size_t)r * per;
+        const bool is_v = o < gv;
+        const float sc = is_v ? s_v : s_t;
+        const __nv_bfloat16 *e = reinterpret_cast<const __nv_bfloat16 *>(&q);
+        __align__(16) __half hv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(__bfloat162float(e[j]) * sc);
+        uint4 *dst = is_v ? reinterpret_cast<uint4 *>(vk) + (size_t)r * gv + o
+                          : reinterpret_cast<uint4 *>(tk) + (size_t)r * gt + (o - gv);
+        *dst = *reinterpret_cast<uint4 *>(hv);
+    };
+    auto src = [&](size_t g) -> const uint4 * {
+        const int r = (int)(g / per);
+        // (L2-only load: another GPU wrote this buffer since the last time this SM may have read it)
+        return reinterpret_cast<const uint4 *>(ps.slot[r] + PEER_HEADER) + (g - (size_t)r * per);
+    };
+    size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; g + 7 * stride < total; g += 8 * stride) {
+        uint4 q[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) q[u] = __ldcg(src(g + u * stride));
+#pragma unroll
+        for (int u = 0; u < 8; ++u) convert(g + u * stride, q[u]);
+    }
+    for (; g < total; g += stride) convert(g, __ldcg(src(g)));
+}
+
+// ----------------------------------------------------------------------------
 // finalize: one warp per owned sample
 // ----------------------------------------------------------------------------
 
@@ -937,17 +1072,14 @@ int backward_impl(const Plan &p, const T *video, const T *text, const float *den
 //             caller reduce-scatters.  4/W GEMM units per rank instead of 6/W for the row+column
 //             block scheme of milnce_forward/backward with n < B.
 // ---------------------------------------------------------------------------------------------
-int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
-                       float *row_lse, float *col_part, float *nom, uint8_t *ws, cudaStream_t st) {
-    int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nom);
-    if (rc) return rc;
-    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+// statistics GEMM over the owned rows + the two merges (everything of the rows-only forward after staging)
+int forward_shard_tail(const Plan &p, float *row_lse, float *col_part, uint8_t *ws, cudaStream_t st) {
     const Operands o = operands(p, ws);
     const __half *vk = o.vk, *tk = o.tk;
     float *pr = reinterpret_cast<float *>(ws + p.off_pr);
     float *pc = reinterpret_cast<float *>(ws + p.off_pc);
-    rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * o.ld_vk,
-                       o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
+    int rc = launch_stats2(p.cg, o.inv_ss, pr, (long long)p.n, pc, p.BK / p.cg, vk + (size_t)p.i0 * o.ld_vk,
+                           o.ld_vk, tk, o.ld_tk, p.n, (int)p.BK, p.D, st, "milnce forward (rows-only shard)");
     if (rc) return rc;
     const MergeFin none{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr};
     merge_partials_kernel<<<(p.n + 31) / 32, 1024, 0, st>>>(pr, nullptr, 1, p.n, p.nb_r, 0, row_lse + p.i0,
@@ -957,6 +1089,13 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
     b200::note_launches(2);
     B200_LAUNCH_OK("milnce shard finalize");
     return 0;
+}
+
+int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
+                       float *row_lse, float *col_part, float *nom, uint8_t *ws, cudaStream_t st) {
+    int rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nom);
+    if (rc) return rc;
+    return forward_shard_tail(p, row_lse, col_part, ws, st);
 }
 
 int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
@@ -1151,6 +1290,69 @@ extern "C" int milnce_forward_shard(const void *video, const void *text, int B, 
     if (rc) return rc;
     return forward_shard_impl(p, (const __nv_bfloat16 *)video, (const __nv_bfloat16 *)text, row_lse,
                               col_part, nom, (uint8_t *)workspace, (cudaStream_t)stream);
+}
+
+extern "C" size_t milnce_peer_slot_bytes(int b, int K, int D) {
+    if (b <= 0 || K <= 0 || D <= 0) return 0;
+    return align_up(PEER_HEADER + (size_t)b * (1 + K) * D * 2, 256);
+}
+
+extern "C" int milnce_peer_publish(const void *video_local, const void *text_local, int b, int K, int D, void *slot,
+                                   float *nom_own, void *stream) {
+    if (!video_local || !text_local || !slot || !nom_own || b <= 0 || K <= 0 || D <= 0) {
+        b200::set_error("milnce_peer_publish: bad argument");
+        return B200HEAD_ERR_ARG;
+    }
+    if (D % 8 != 0 || ((((uintptr_t)video_local) | ((uintptr_t)text_local) | ((uintptr_t)slot)) & 15)) {
+        b200::set_error("milnce_peer_publish: D must be a multiple of 8 and all pointers 16-byte aligned");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    B200_CUDA_OK(cudaMemsetAsync(slot, 0, PEER_HEADER, st));
+    const int wpb = 8;
+    const int blocks = std::min((b + wpb - 1) / wpb, 8 * num_sms());
+    peer_publish_kernel<<<blocks, wpb * 32, 0, st>>>((const __nv_bfloat16 *)video_local, (const __nv_bfloat16 *)text_local,
+                                                     b, K, D, (uint8_t *)slot, nom_own);
+    b200::note_launches(1);
+    B200_LAUNCH_OK("milnce_peer_publish");
+    return 0;
+}
+
+extern "C" int milnce_forward_shard_peers(const void *const *slots, int W, int B, int K, int D, int i0, int n,
+                                          float *row_lse, float *col_part, void *workspace, size_t workspace_bytes,
+                                          void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, B200HEAD_BF16, i0, n)) {
+        b200::set_error("milnce_forward_shard_peers: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!slots || !row_lse || !col_part || W < 1 || W > PEER_MAX || B % W != 0) {
+        b200::set_error("milnce_forward_shard_peers: bad argument (1 <= W <= %d ranks, B a multiple of W)", PEER_MAX);
+        return B200HEAD_ERR_ARG;
+    }
+    const int b = B / W;
+    if (b % 64 != 0 || D % 8 != 0 || n != b || i0 % b != 0) {
+        b200::set_error("milnce_forward_shard_peers: the local batch must be a multiple of 64, D of 8, and the "
+                        "range one rank's shard");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *ws = (uint8_t *)workspace;
+    Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
+    B200_CUDA_OK(cudaMemsetAsync(sc, 0, sizeof(Scalars), st));
+    PeerSlots ps;
+    for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)slots[r < W ? r : 0];
+    __half *vk = reinterpret_cast<__half *>(ws + p.off_vk), *tk = reinterpret_cast<__half *>(ws + p.off_tk);
+    stage_peers_kernel<<<4 * num_sms(), 256, 0, st>>>(ps, W, b, K, D, vk, tk, sc);   // ld_vk == ld_tk == D (D % 8 == 0)
+    b200::note_launches(1);
+    B200_LAUNCH_OK("milnce_forward_shard_peers staging");
+    return forward_shard_tail(p, row_lse, col_part, ws, st);
 }
 
 extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom,

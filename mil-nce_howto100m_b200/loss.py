@@ -105,6 +105,32 @@ class CudaBackend:
         return pack, ws
 
     @staticmethod
+    def forward_shard_peers(ring, video_local, text_local, world, rank):
+        """The rows-only forward without an embedding collective (see PeerRing in utils.py and
+        include/b200head.h, milnce_forward_shard_peers).  Returns (pack, ws) like forward_shard."""
+        lib = _lib.load()
+        b, D = video_local.shape
+        K = text_local.shape[0] // b
+        B = world * b
+        i0 = rank * b
+        dev = video_local.device
+        nbytes = lib.milnce_workspace_bytes(B, K, D, _lib.BF16, b)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        pack = torch.empty(2 * b + B, dtype=torch.float32, device=dev)
+        slot_ptr, peer_ptrs = ring.next_slot()
+        with torch.cuda.device(dev):
+            st = _lib.stream_ptr(dev)
+            rc = lib.milnce_peer_publish(_ptr(video_local), _ptr(text_local), b, K, D, ctypes.c_void_p(slot_ptr),
+                                         ctypes.c_void_p(pack.data_ptr() + 4 * b), st)
+            _lib.check(rc, "milnce_peer_publish")
+            ring.barrier()      # every rank's slot is complete (and nobody still reads the slot written next step)
+            arr = (ctypes.c_void_p * world)(*peer_ptrs)
+            rc = lib.milnce_forward_shard_peers(arr, world, B, K, D, i0, b, ctypes.c_void_p(pack.data_ptr() - 4 * i0),
+                                                ctypes.c_void_p(pack.data_ptr() + 8 * b), _ptr(ws), nbytes, st)
+            _lib.check(rc, "milnce_forward_shard_peers")
+        return pack, ws
+
+    @staticmethod
     def shard_combine(gathered, world, b):
         """(den[B], nom[B], loss) from the all-gathered (W, 2b + B) statistics of forward_shard."""
         lib = _lib.load()
@@ -121,14 +147,19 @@ class CudaBackend:
 
     @staticmethod
     def backward_shard(video, text, den, nom, grad_loss, i0, n, ws, parts=3, grad_dtype=torch.float32,
-                       partial_dtype=torch.float32):
+                       partial_dtype=torch.float32, dims=None):
         """Returns (dvideo (n, D) in grad_dtype or None, dtext_partial (B*K, D) in partial_dtype or None).
 
         parts=1: gradient tiles + dtext_partial only; parts=2: dvideo only, from the workspace a
         parts=1 call left; parts=3: both.  dtext_partial is to be reduce-scattered."""
         lib = _lib.load()
-        B, D = video.shape
-        K = text.shape[0] // B
+        if dims is not None:        # (B, K, D) given explicitly: video / text are then only the local shards
+            B, K, D = dims          # and are not read (the workspace of the forward holds the operands)
+            if ws is None:
+                raise ValueError("explicit dims need the workspace of the forward")
+        else:
+            B, D = video.shape
+            K = text.shape[0] // B
         code = _dtype_code(video)
         dev = video.device
         reuse = 1

@@ -74,6 +74,35 @@ def _gather_embeddings(v, t, world, group):
     return V, T
 
 
+class PeerRing:
+    """This rank's slot in peer-mapped ("symmetric") memory plus the peers' views of theirs.
+
+    The rows scheme can then skip the NCCL all-gather of the embeddings: every rank copies its shard into
+    its slot (milnce_peer_publish), the ranks meet at a device-side barrier, and the staging kernel reads
+    all shards straight from the peers' slots over NVLink (milnce_forward_shard_peers).  One slot, two
+    barriers per step: the first keeps a fast rank from overwriting a slot that a slow peer is still
+    reading from the previous step, the second says that every slot is complete.  (Barriers are kernels on
+    the current stream, so the sequence can be captured in a CUDA graph.)"""
+
+    def __init__(self, b, K, D, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _lib
+        lib = _lib.load()
+        self.slot_bytes = int(lib.milnce_peer_slot_bytes(b, K, D))
+        self.buf = symm_mem.empty(self.slot_bytes, dtype=torch.uint8, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.rank = int(self.hdl.rank)
+        self.shape = (b, K, D)
+
+    def next_slot(self):
+        self.hdl.barrier(channel=0)          # nobody is still reading the slots of the previous step
+        return self.ptrs[self.rank], list(self.ptrs)
+
+    def barrier(self):
+        self.hdl.barrier(channel=0)          # every rank has published
+
+
 def _mark(marks, name, dev):
     """Phase stamp for the timeline tool (profiles/multi_timeline.py); a no-op in normal use."""
     if marks is not None:
@@ -145,13 +174,20 @@ class _GatheredMILNCERows(torch.autograd.Function):
         t = text_local.detach().contiguous()
         marks = opts.get("marks")
         _mark(marks, "start", v.device)
-        V, T = _gather_embeddings(v, t, world, group)
-        _mark(marks, "gather_embeddings", v.device)
         B = world * b
         i0 = rank * b
-        # the kernels write [row_lse of my samples | nom of my samples | my column partials] in place
-        pack, ws = backend.forward_shard(V, T, i0, b)
-        _mark(marks, "forward_kernels", v.device)
+        ring = opts.get("ring")
+        if ring is not None:
+            # no embedding collective: publish the shard, meet, stage all shards from the peers' memory
+            pack, ws = backend.forward_shard_peers(ring, v, t, world, rank)
+            V, T = v, t                      # (only their shapes are used from here on)
+            _mark(marks, "publish+stage+forward_kernels", v.device)
+        else:
+            V, T = _gather_embeddings(v, t, world, group)
+            _mark(marks, "gather_embeddings", v.device)
+            # the kernels write [row_lse of my samples | nom of my samples | my column partials] in place
+            pack, ws = backend.forward_shard(V, T, i0, b)
+            _mark(marks, "forward_kernels", v.device)
         allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
         dist.all_gather_into_tensor(allp, pack, group=group)
         _mark(marks, "stats_exchange", v.device)
@@ -159,13 +195,14 @@ class _GatheredMILNCERows(torch.autograd.Function):
         _mark(marks, "combine", v.device)
         ctx.save_for_backward(V, T, den, nom_all)
         ctx.ws = ws
-        ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0], marks, opts.get("partial_dtype"))
+        ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0], marks, opts.get("partial_dtype"),
+                    (B, t.shape[0] // b, v.shape[1]))
         return loss
 
     @staticmethod
     def backward(ctx, grad_output):
         V, T, den, nom = ctx.saved_tensors
-        i0, b, backend, vdt, tdt, group, bk_local, marks, pdt = ctx.meta
+        i0, b, backend, vdt, tdt, group, bk_local, marks, pdt, dims = ctx.meta
         _mark(marks, "backward_start", V.device)
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
         # default: partials in the embeddings' own 16-bit dtype - the result is rounded to that dtype anyway, and
@@ -173,11 +210,11 @@ class _GatheredMILNCERows(torch.autograd.Function):
         # (profiles/r2_multi_timeline_*.txt); float32 on request (partial_dtype=torch.float32)
         pdt = pdt if pdt is not None else (torch.bfloat16 if tdt == torch.bfloat16 else torch.float32)
         # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
-        _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt)
+        _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt, dims=dims)
         _mark(marks, "gradient_tiles+dtext_partial", V.device)
         dt = torch.empty((bk_local, dt_partial.shape[1]), dtype=dt_partial.dtype, device=dt_partial.device)
         work = dist.reduce_scatter_tensor(dt, dt_partial, op=dist.ReduceOp.SUM, group=group, async_op=True)
-        dv, _ = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=2, grad_dtype=vdt)
+        dv, _ = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=2, grad_dtype=vdt, dims=dims)
         ctx.ws = None
         _mark(marks, "dvideo", V.device)
         work.wait()
@@ -194,16 +231,26 @@ class GatheredMILNCELoss(torch.nn.Module):
     embeddings of this rank.
     """
 
-    def __init__(self, args=None, group=None, scheme="auto", partial_dtype=None, _backend=None):
+    def __init__(self, args=None, group=None, scheme="auto", partial_dtype=None, gather="auto", _backend=None):
         """scheme: "rows" (each rank computes only its rows of S, reduce-scatter of the text
         gradient; bf16 embeddings), "rowcol" (row block + column block per rank, no gradient
         collective - the reference's communication pattern), or "auto" (rows when available).
         partial_dtype: dtype of the rows scheme's text-gradient partials on the wire (default: the
         embeddings' dtype, i.e. bfloat16; torch.float32 doubles the reduce-scatter payload).
+        gather: how the rows scheme obtains the other ranks' embeddings - "nccl" (one grouped all-gather),
+        "peer" (no collective: shards are read from the peers' memory, see PeerRing; needs CUDA bf16
+        embeddings, a local batch that is a multiple of 64, D a multiple of 8, at most 16 ranks), or
+        "auto" (peer when those conditions hold and symmetric memory can be set up, else nccl).
         _backend: private test seam (the CPU tests drive the orchestration with a stand-in)."""
         super().__init__()
         if scheme not in ("auto", "rows", "rowcol"):
             raise ValueError("scheme must be 'auto', 'rows' or 'rowcol'")
+        if gather not in ("auto", "nccl", "peer"):
+            raise ValueError("gather must be 'auto', 'nccl' or 'peer'")
+        self.gather = gather
+        self._ring = None
+        self._ring_failed = False
+        self.last_gather = None
         self.args = args
         self.group = group
         self._backend = _backend
@@ -228,8 +275,37 @@ class GatheredMILNCELoss(torch.nn.Module):
             use_rows = ok
         self.last_scheme = "rows" if use_rows else ("rowcol" if world > 1 else "single")
         fn = _GatheredMILNCERows if use_rows else _GatheredMILNCE
-        opts = {"marks": self._marks, "partial_dtype": self.partial_dtype}
+        ring = self._peer_ring(video_embd, text_embd, world) if (use_rows and self._backend is None) else None
+        self.last_gather = "peer" if ring is not None else ("nccl" if world > 1 else None)
+        opts = {"marks": self._marks, "partial_dtype": self.partial_dtype, "ring": ring}
         return fn.apply(video_embd, text_embd, world, rank, self.group, backend, opts)
+
+
+def _peer_ring(self, video_embd, text_embd, world):
+    """The PeerRing for these shapes, or None when the peer path does not apply (see `gather`)."""
+    if self.gather == "nccl" or self._ring_failed:
+        return None
+    b, D = video_embd.shape
+    K = text_embd.shape[0] // max(b, 1)
+    ok = (video_embd.is_cuda and video_embd.dtype == torch.bfloat16 and b % 64 == 0 and D % 8 == 0 and world <= 16
+          and dist.get_backend(self.group if self.group is not None else dist.group.WORLD) == "nccl")
+    if not ok:
+        if self.gather == "peer":
+            raise RuntimeError("gather='peer' needs CUDA bfloat16 embeddings, a local batch that is a multiple of 64, "
+                               "D a multiple of 8, at most 16 ranks and the NCCL backend")
+        return None
+    if self._ring is None or self._ring.shape != (b, K, D):
+        try:
+            self._ring = PeerRing(b, K, D, video_embd.device, self.group)
+        except Exception:
+            if self.gather == "peer":
+                raise
+            self._ring_failed = True        # symmetric memory is not available here: stay on NCCL
+            return None
+    return self._ring
+
+
+GatheredMILNCELoss._peer_ring = _peer_ring
 
 
 class GraphedGatheredMILNCEStep:
@@ -251,11 +327,11 @@ class GraphedGatheredMILNCEStep:
     """
 
     def __init__(self, b, K, D, dtype=torch.bfloat16, device=None, group=None, scheme="auto",
-                 partial_dtype=None, warmup=3):
+                 partial_dtype=None, gather="auto", warmup=3):
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.video = torch.zeros(b, D, dtype=dtype, device=dev).requires_grad_(True)
         self.text = torch.zeros(b * K, D, dtype=dtype, device=dev).requires_grad_(True)
-        self.module = GatheredMILNCELoss(group=group, scheme=scheme, partial_dtype=partial_dtype)
+        self.module = GatheredMILNCELoss(group=group, scheme=scheme, partial_dtype=partial_dtype, gather=gather)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):       # warm-up off the capture: communicators, library, allocator

@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--batch", type=int, default=8192)
+    ap.add_argument("--only", default=None, help="run only the variants whose name contains this")
     args = ap.parse_args()
     import milnce_b200
     world = int(os.environ["WORLD_SIZE"])
@@ -45,9 +46,12 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return tt.tolist()
 
-    variants = [("rows/f32-partial", dict(scheme="rows", partial_dtype=torch.float32)),
-                ("rows/bf16-partial", dict(scheme="rows", partial_dtype=torch.bfloat16)),
+    variants = [("rows/f32-partial", dict(scheme="rows", partial_dtype=torch.float32, gather="nccl")),
+                ("rows/bf16-partial", dict(scheme="rows", partial_dtype=torch.bfloat16, gather="nccl")),
+                ("rows/bf16-partial/peer-memory gather", dict(scheme="rows", partial_dtype=torch.bfloat16, gather="peer")),
                 ("rowcol", dict(scheme="rowcol"))]
+    if args.only:
+        variants = [v for v in variants if args.only in v[0]]
     for name, kw in variants:
         mod = milnce_b200.GatheredMILNCELoss(**kw)
         for _ in range(5):

@@ -92,7 +92,7 @@ class OracleBackend:
         return den, nom_all, (den - nom_all).mean()
 
     @staticmethod
-    def backward_shard(V, T, den, nom, g, i0, n, ws, parts=3, grad_dtype=None, partial_dtype=None):
+    def backward_shard(V, T, den, nom, g, i0, n, ws, parts=3, grad_dtype=None, partial_dtype=None, dims=None):
         v = V.double().numpy()
         t = T.double().numpy()
         B = v.shape[0]

@@ -25,7 +25,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, scheme, out):
+def _worker(rank, world, port, scheme, out, gather="nccl"):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -40,8 +40,18 @@ def _worker(rank, world, port, scheme, out):
         T = (torch.randn(B * K, D, generator=g) * 0.1).bfloat16().cuda()
         v_loc = V[rank * b:(rank + 1) * b].clone().requires_grad_(True)
         t_loc = T[rank * b * K:(rank + 1) * b * K].clone().requires_grad_(True)
-        loss = milnce_b200.GatheredMILNCELoss(scheme=scheme)(v_loc, t_loc)
+        mod = milnce_b200.GatheredMILNCELoss(scheme=scheme, gather=gather)
+        loss = mod(v_loc, t_loc)
         loss.backward()
+        if gather == "peer":
+            assert mod.last_gather == "peer"
+            # a second step through the same ring (slot reuse, barriers) must give the same result
+            g1 = v_loc.grad.clone()
+            v_loc.grad = None
+            t_loc.grad = None
+            loss = mod(v_loc, t_loc)
+            loss.backward()
+            assert torch.equal(g1, v_loc.grad)
         Vf = V.clone().requires_grad_(True)
         Tf = T.clone().requires_grad_(True)
         ref = milnce_b200.MILNCELoss()(Vf, Tf)
@@ -69,7 +79,7 @@ def test_gathered_loss_two_gpus_nccl(scheme):
     assert list(out) == [1] * world
 
 
-def _worker_graphed(rank, world, port, out):
+def _worker_graphed(rank, world, port, out, gather="nccl"):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -79,7 +89,7 @@ def _worker_graphed(rank, world, port, out):
         import milnce_b200
         B, K, D = 1024, 4, 512
         b = B // world
-        step = milnce_b200.GraphedGatheredMILNCEStep(b, K, D, scheme="rows", partial_dtype=torch.bfloat16)
+        step = milnce_b200.GraphedGatheredMILNCEStep(b, K, D, scheme="rows", partial_dtype=torch.bfloat16, gather=gather)
         ok = True
         for seed in (5, 6):     # two replays on different inputs
             g = torch.Generator().manual_seed(seed)
@@ -112,4 +122,24 @@ def test_graphed_gathered_step_two_gpus_nccl():
     world = 2
     out = mp.get_context("spawn").Array("i", [0] * world)
     mp.spawn(_worker_graphed, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert list(out) == [1] * world
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.timeout(240)
+def test_gathered_loss_peer_memory_two_gpus():
+    """gather="peer": no embedding all-gather; the shards are published in symmetric memory and staged from the
+    peers' buffers (milnce_peer_publish / milnce_forward_shard_peers)."""
+    world = 2
+    out = mp.get_context("spawn").Array("i", [0] * world)
+    mp.spawn(_worker, args=(world, _free_port(), "rows", out, "peer"), nprocs=world, join=True)
+    assert list(out) == [1] * world
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.timeout(240)
+def test_graphed_gathered_step_peer_memory_two_gpus():
+    world = 2
+    out = mp.get_context("spawn").Array("i", [0] * world)
+    mp.spawn(_worker_graphed, args=(world, _free_port(), out, "peer"), nprocs=world, join=True)
     assert list(out) == [1] * world
