@@ -636,6 +636,22 @@ def bench_sdtw(dev, pk, args, world, rank, barrier, max_over_ranks):
            "roofline": {"bound": "hbm", "achieved": alg_bytes / (ms * 1e-3) / 1e9, "peak": pk["hbm"] * world,
                         "unit": "GB/s", "frac": alg_bytes / (ms * 1e-3) / 1e9 / (pk["hbm"] * world),
                         "traffic": traffic.get("sdtw_step_dram_bytes")}}
+    if world == 1:
+        # the general path (soft_dtw_cuda.py's own use: euclidean, longer sequences): eager, events, fwd+bwd
+        gen = []
+        for (bp, n, m, dd) in ((64, 256, 256, 64), (8, 1024, 1024, 64)):
+            gx = torch.randn(bp, n, dd, device=dev).requires_grad_(True)
+            gy = torch.randn(bp, m, dd, device=dev).requires_grad_(True)
+            gmod = milnce_b200.SoftDTW(True, gamma=1.0, dist_func="euclidean")
+
+            def gstep():
+                gx.grad = None
+                gy.grad = None
+                gmod(gx, gy).sum().backward()
+            gsec = timed(gstep, 10, 3, barrier) / 10
+            gen.append({"pairs": bp, "N": n, "M": m, "d": dd, "dist_func": "euclidean", "gamma": 1.0,
+                        "ms_per_step": gsec * 1e3, "cells_per_s": 2.0 * bp * n * m / gsec})
+        out["general"] = gen
     if rank == 0 and world == 1 and not args.no_cpu:
         val, s, kind, note = cpu_sdtw(Bp, N, M, d)
         out["cpu_baseline"] = {"value": val, "unit": "cells/s", "cores": host_threads(), "kind": kind,

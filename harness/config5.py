@@ -15,8 +15,9 @@ swapped is the three-line loss head of the train step (main_distributed.py:233-2
     arm "b200":       GatheredMILNCELoss (all-gather + sharded loss + local gradient slices in one module),
                       the loss stays on the device and is read every `--display` steps
 
-Both arms run the same model, the same optimiser and the same inputs under bf16 autocast; the first
-step of each arm starts from identical weights, and its loss and embedding gradients are compared.
+Both arms run the same model, the same optimiser and the same inputs under bf16 autocast.  Parity of the
+head is checked on the embeddings the towers emit, against the reference's head evaluated in float32 on
+those same values (under autocast the reference rounds its logits to bf16, which is reported beside it).
 Prints one JSON line (rank 0): step time of both arms, the time of the loss head inside the step, its
 share, and the parity errors.  TEST / BENCH INFRASTRUCTURE: this file uses oracle/_ref.
 """
@@ -146,11 +147,40 @@ def main():
         torch.cuda.empty_cache()
         return sum(times) / len(times), sum(head_times) / len(head_times), first
 
-    t_ref, h_ref, f_ref = run_arm(head_reference, 1)
-    t_our, h_our, f_our = run_arm(head_b200, args.display)
-
     def rel(x, y):
         return ((x.double() - y.double()).norm() / y.double().norm().clamp_min(1e-30)).item()
+
+    # Parity of the loss head on the embeddings the towers emit (bf16 under autocast).  The yardstick is the
+    # reference's own head evaluated in float32 on those same bf16 values; the reference arm AS RUN (autocast:
+    # its matmul rounds the logits to bf16, loss.py:11) is reported next to it - its distance to that yardstick
+    # is the noise floor of the comparison between the two arms' first steps below.
+    with torch.no_grad():
+        ve0, te0 = towers(model0)
+
+    def head_grads(head, ve, te, autocast):
+        ve = ve.detach().clone().requires_grad_(True)
+        te = te.detach().clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            loss = head(ve, te)
+        loss.backward()
+        return loss.item(), ve.grad.float(), te.grad.float()
+
+    y_loss, y_dv, y_dt = head_grads(head_reference, ve0.float(), te0.float(), False)
+    o_loss, o_dv, o_dt = head_grads(head_b200, ve0, te0, True)
+    r_loss, r_dv, r_dt = head_grads(head_reference, ve0, te0, True)
+    head_parity = {
+        "b200_vs_reference_head_in_float32": {"loss_rel": abs(o_loss - y_loss) / abs(y_loss),
+                                              "dvideo_embd_rel": rel(o_dv, y_dv), "dtext_embd_rel": rel(o_dt, y_dt)},
+        "reference_under_autocast_vs_same": {"loss_rel": abs(r_loss - y_loss) / abs(y_loss),
+                                             "dvideo_embd_rel": rel(r_dv, y_dv), "dtext_embd_rel": rel(r_dt, y_dt)},
+        "tolerance": {"loss_rel": 1e-5, "grad_rel": 5e-3,
+                      "note": "gradients are returned in the embeddings' dtype (bf16): one rounding, 2^-9 per element"},
+    }
+    hp = head_parity["b200_vs_reference_head_in_float32"]
+    ok = hp["loss_rel"] < 1e-5 and hp["dvideo_embd_rel"] < 5e-3 and hp["dtext_embd_rel"] < 5e-3
+
+    t_ref, h_ref, f_ref = run_arm(head_reference, 1)
+    t_our, h_our, f_our = run_arm(head_b200, args.display)
 
     out = {
         "config": 5, "workload": f"S3D-G MIL-NCE train step, {args.frames}x{args.size}x{args.size} clips, "
@@ -162,11 +192,11 @@ def main():
                      "head": f"GatheredMILNCELoss, loss read every {args.display} steps"},
         "step_speedup": t_ref / t_our, "loss_head_forward_share_reference": h_ref / t_ref,
         "loss_head_forward_share_b200": h_our / t_our,
-        "parity_first_step": {"loss_rel": abs(f_our[0] - f_ref[0]) / abs(f_ref[0]),
-                              "dvideo_embd_rel": rel(f_our[1], f_ref[1]), "dtext_embd_rel": rel(f_our[2], f_ref[2])},
+        "head_parity": head_parity,
+        "first_step_arm_vs_arm": {"loss_rel": abs(f_our[0] - f_ref[0]) / abs(f_ref[0]),
+                                  "dvideo_embd_rel": rel(f_our[1], f_ref[1]), "dtext_embd_rel": rel(f_our[2], f_ref[2]),
+                                  "note": "informational: the reference arm rounds its logits to bf16 under autocast"},
     }
-    ok = (out["parity_first_step"]["loss_rel"] < 1e-3 and out["parity_first_step"]["dvideo_embd_rel"] < 1e-2
-          and out["parity_first_step"]["dtext_embd_rel"] < 1e-2)
     out["parity_ok"] = bool(ok)
     if rank == 0:
         print(json.dumps(out), flush=True)

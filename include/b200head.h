@@ -116,6 +116,11 @@ int milnce_forward_shard(const void *video, const void *text, int B, int K, int 
  * similarity matrix is reduced on every rank, loss.py:16-18.) */
 int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom, float *loss,
                          void *stream);
+/* The same, with the W packs read where they are: packs[r] = rank r's (2b + B) floats as mapped into this
+ * process (host array of W device pointers), e.g. in peer-mapped memory after the caller's cross-rank
+ * barrier - the all-gather of the statistics is then not needed.  W <= 16 for both variants. */
+int milnce_shard_combine_peers(const void *const *packs, int W, int b, float *den, float *nom, float *loss,
+                               void *stream);
 /* Rows-only sharding WITHOUT an embedding collective.  Every rank publishes its bfloat16 shard in a buffer
  * that its peers can read directly (peer-mapped memory, e.g. torch symmetric memory: slot pointers of all
  * ranks are exchanged once at set-up), and stages the fp16 operands of all W ranks straight from the
@@ -124,8 +129,9 @@ int milnce_shard_combine(const float *gathered, int W, int b, float *den, float 
  *   milnce_peer_publish      copies the local shard into this rank's slot (milnce_peer_slot_bytes), leaves
  *                            |video|max, |text|max in the slot header and nom[0, b) of the local samples;
  *   <the caller's cross-rank barrier: every slot is complete>
- *   milnce_forward_shard_peers  reads all slots (slots[r] = rank r's slot as mapped into THIS process),
- *                            then as milnce_forward_shard: row_lse[i0, i0+n), col_part[0, B).
+ *   milnce_forward_shard_peers  reads the text of all slots and the video of its own (slots[r] = rank r's
+ *                            slot as mapped into THIS process), then as milnce_forward_shard:
+ *                            row_lse[i0, i0+n), col_part[0, B).
  * Backward: milnce_backward_shard with reuse_forward_ws = 1 (it reads only the workspace).  The caller must
  * not let a rank overwrite its slot while a peer may still be reading it (two slots used alternately and the
  * per-step barrier are enough).  Needs b = B / W a multiple of 64, D a multiple of 8, W <= 16. */
@@ -135,6 +141,25 @@ int milnce_peer_publish(const void *video_local, const void *text_local, int b, 
 int milnce_forward_shard_peers(const void *const *host_slots, int W, int B, int K, int D, int i0, int n,
                                float *row_lse, float *col_part, void *workspace, size_t workspace_bytes,
                                void *stream);
+/* parts = 1 of milnce_backward_shard (gradient tiles + partial text gradient, from the workspace the forward
+ * left), with the partial DELIVERED instead of stored: the b*K rows of the (B*K, D) partial that rank q owns are
+ * written as bfloat16 to owner_dst[q] (host array of W device pointers, each a (b*K, D) buffer, normally in
+ * rank q's peer-mapped memory: this rank's block of q's receive area) by the GEMM epilogue's own stores, so the
+ * transfer of the reduce-scatter overlaps the GEMM.  Afterwards: milnce_backward_shard(parts = 2) for dvideo,
+ * the caller's cross-rank barrier, and milnce_peer_reduce_dtext over the W blocks each rank received
+ * (partials[q] = block q, rank = 0).  b*K must be a multiple of 128, W <= 16. */
+int milnce_backward_shard_push(const float *den, const float *nom, const float *grad_loss, void *const *owner_dst,
+                               int W, int B, int K, int D, int i0, int n, void *workspace, size_t workspace_bytes,
+                               void *stream);
+/* The gradient collective of the rows-only scheme by pull, for callers whose partial text gradients sit in
+ * peer-mapped memory (it replaces reduce_scatter(sum) of dtext_partial; reference counterpart: autograd of
+ * the concatenated text tensor + the slice of utils.py:20-24).  partials[r] = rank r's (B*K, D) BFLOAT16
+ * dtext_partial as mapped into this process (host array of W device pointers; write it with
+ * milnce_backward_shard(parts = 1, dtext_dtype = BF16) and pass the caller's cross-rank barrier first).
+ * dtext (b*K, D), float32 or bfloat16 = sum over r of rows [rank*b*K, (rank+1)*b*K) of partials[r], added in
+ * rank order in float32: bit-identical from run to run.  W <= 16, b*K*D a multiple of 8. */
+int milnce_peer_reduce_dtext(const void *const *partials, int W, int rank, int b, int K, int D, void *dtext,
+                             int dtext_dtype, void *stream);
 int milnce_backward_shard(const void *video, const void *text, const float *den, const float *nom,
                           const float *grad_loss, void *dvideo, int dvideo_dtype, void *dtext_partial,
                           int dtext_dtype, int parts, int B, int K, int D, int dtype, int i0, int n,

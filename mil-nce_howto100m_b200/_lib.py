@@ -101,6 +101,12 @@ def _declare(lib):
     lib.milnce_peer_publish.argtypes = [vp, vp, i32, i32, i32, vp, fp, vp]
     lib.milnce_forward_shard_peers.restype = i32
     lib.milnce_forward_shard_peers.argtypes = [c.POINTER(c.c_void_p), i32, i32, i32, i32, i32, i32, fp, fp, vp, sz, vp]
+    lib.milnce_backward_shard_push.restype = i32
+    lib.milnce_backward_shard_push.argtypes = [fp, fp, fp, c.POINTER(c.c_void_p), i32, i32, i32, i32, i32, i32, vp, sz, vp]
+    lib.milnce_peer_reduce_dtext.restype = i32
+    lib.milnce_peer_reduce_dtext.argtypes = [c.POINTER(c.c_void_p), i32, i32, i32, i32, i32, vp, i32, vp]
+    lib.milnce_shard_combine_peers.restype = i32
+    lib.milnce_shard_combine_peers.argtypes = [c.POINTER(c.c_void_p), i32, i32, fp, fp, fp, vp]
     lib.milnce_shard_combine.restype = i32
     lib.milnce_shard_combine.argtypes = [fp, i32, i32, fp, fp, fp, vp]
     lib.milnce_backward_shard.restype = i32

@@ -481,14 +481,16 @@ peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16
     }
 }
 
-// bf16 shards of all W ranks -> scaled fp16 K-major operands in the local workspace.  The power-of-two
-// scales come from the maximum over the W slot headers; block 0 publishes them for the later kernels.
-// D % 8 == 0, so the staged rows are unpadded and both tensors are flat arrays: a grid-stride loop over
-// 16-byte granules, eight independent loads in flight per thread, 512 contiguous bytes per warp
-// instruction.  (A 64 x 64-tile version with two loads per thread read the peers at 95 GB/s.)
+// bf16 shards -> scaled fp16 K-major operands in the local workspace: the text of ALL W ranks (the B operand of
+// the similarity pass and of dvideo) and the video of THIS rank only (the rows scheme never touches the other
+// ranks' video rows, so they do not cross NVLink).  The power-of-two scales come from the maximum over the W
+// slot headers; block 0 publishes them for the later kernels.  D % 8 == 0, so the staged rows are unpadded and
+// both tensors are flat arrays: a grid-stride loop over 16-byte granules, eight independent loads in flight
+// per thread, 512 contiguous bytes per warp instruction.  (A 64 x 64-tile version with two loads per thread
+// read the peers at 95 GB/s.)
 __global__ void __launch_bounds__(256)
-stage_peers_kernel(PeerSlots ps, int W, int b, int K, int D, __half *__restrict__ vk, __half *__restrict__ tk,
-                   Scalars *scal) {
+stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *__restrict__ vk,
+                   __half *__restrict__ tk, Scalars *scal) {
     unsigned int av = 0, at = 0;
     for (int r = 0; r < W; ++r) {
         const unsigned int *h = reinterpret_cast<const unsigned int *>(ps.slot[r]);
@@ -504,25 +506,24 @@ stage_peers_kernel(PeerSlots ps, int W, int b, int K, int D, __half *__restrict_
         scal->inv_ss = (1.f / s_v) * (1.f / s_t);
     }
     const size_t gv = (size_t)b * D / 8, gt = gv * K;      // granules (8 elements) per shard: video, text
-    const size_t per = gv + gt, total = per * W;
+    const size_t n_text = gt * W, total = n_text + gv;     // [text of rank 0 .. W-1 | own video]
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     auto convert = [&](size_t g, const uint4 &q) {
-        const int r = (int)(g / per);
-        const size_t o = g - (size_t)r * per;
-        const bool is_v = o < gv;
+        const bool is_v = g >= n_text;
         const float sc = is_v ? s_v : s_t;
         const __nv_bfloat16 *e = reinterpret_cast<const __nv_bfloat16 *>(&q);
         __align__(16) __half hv[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(__bfloat162float(e[j]) * sc);
-        uint4 *dst = is_v ? reinterpret_cast<uint4 *>(vk) + (size_t)r * gv + o
-                          : reinterpret_cast<uint4 *>(tk) + (size_t)r * gt + (o - gv);
+        uint4 *dst = is_v ? reinterpret_cast<uint4 *>(vk) + (size_t)rank * gv + (g - n_text)
+                          : reinterpret_cast<uint4 *>(tk) + g;
         *dst = *reinterpret_cast<uint4 *>(hv);
     };
     auto src = [&](size_t g) -> const uint4 * {
-        const int r = (int)(g / per);
-        // (L2-only load: another GPU wrote this buffer since the last time this SM may have read it)
-        return reinterpret_cast<const uint4 *>(ps.slot[r] + PEER_HEADER) + (g - (size_t)r * per);
+        // (L2-only loads: another GPU wrote this buffer since the last time this SM may have read it)
+        if (g >= n_text) return reinterpret_cast<const uint4 *>(ps.slot[rank] + PEER_HEADER) + (g - n_text);
+        const int r = (int)(g / gt);
+        return reinterpret_cast<const uint4 *>(ps.slot[r] + PEER_HEADER) + gv + (g - (size_t)r * gt);
     };
     size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     for (; g + 7 * stride < total; g += 8 * stride) {
@@ -533,6 +534,47 @@ stage_peers_kernel(PeerSlots ps, int W, int b, int K, int D, __half *__restrict_
         for (int u = 0; u < 8; ++u) convert(g + u * stride, q[u]);
     }
     for (; g < total; g += stride) convert(g, __ldcg(src(g)));
+}
+
+// Reduce-scatter of the partial text gradient by PULL: every rank left its (B*K, D) bf16 partial in a buffer its
+// peers can read; this rank sums block `rank` (its own b*K rows) of all W partials, in rank order, in float32
+// (so the result does not depend on timing), and writes its dtext.  Plain 16-byte loads over NVLink.
+template <bool OUT_BF16>
+__global__ void __launch_bounds__(256)
+peer_reduce_kernel(PeerSlots parts, int W, size_t first, size_t count, void *__restrict__ out) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < count; g += stride) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int r0 = 0; r0 < W; r0 += 4) {
+            uint4 q[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (r0 + u < W) q[u] = __ldcg(reinterpret_cast<const uint4 *>(parts.slot[r0 + u]) + first + g);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r0 + u >= W) break;
+                const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&q[u]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 v = __bfloat1622float2(h[j]);
+                    acc[2 * j] += v.x;
+                    acc[2 * j + 1] += v.y;
+                }
+            }
+        }
+        if (OUT_BF16) {
+            __nv_bfloat162 h[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+            reinterpret_cast<uint4 *>(out)[g] = *reinterpret_cast<uint4 *>(h);
+        } else {
+            float4 *o = reinterpret_cast<float4 *>(out) + 2 * g;
+            o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        }
+    }
 }
 
 // ----------------------------------------------------------------------------
@@ -688,26 +730,34 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
     if (lane == 0) nom[i] = pm + logf(ps);
 }
 
-// Rows-only sharding, after the exchange: allp is (W, 2b + B) = per rank [row_lse of its b samples |
-// nom of its b samples | its partial column statistic of all B samples].  One block:
+// Rows-only sharding, after the exchange: pack r (2b + B floats) = rank r's [row_lse of its b samples |
+// nom of its b samples | its partial column statistic of all B samples]; the packs are either the rows of one
+// all-gathered array or W separate buffers in the ranks' peer-readable memory.  One block:
 //   den_j = logaddexp(row_j, logsumexp_r col_part[r][j]), nom_all, loss = mean(den - nom)
 // (replaces a cat / logsumexp / logaddexp / mean chain of eight small torch launches).
 __global__ void __launch_bounds__(1024)
-shard_combine_kernel(const float *__restrict__ allp, int W, int b, int B, float *__restrict__ den,
+shard_combine_kernel(PeerSlots packs, int W, int b, int B, float *__restrict__ den,
                      float *__restrict__ nom_all, float *__restrict__ loss) {
     __shared__ double sh[32];
-    const size_t ld = (size_t)2 * b + B;
     double acc = 0.0;
     for (int j = threadIdx.x; j < B; j += blockDim.x) {
         const int r = j / b, i = j - r * b;
-        const float row = allp[(size_t)r * ld + i];
-        const float nm = allp[(size_t)r * ld + b + i];
+        const float *own = reinterpret_cast<const float *>(packs.slot[r]);
+        const float row = __ldcg(own + i);
+        const float nm = __ldcg(own + b + i);
+        float cp[PEER_MAX];
+#pragma unroll
+        for (int w = 0; w < PEER_MAX; ++w)
+            cp[w] = w < W ? __ldcg(reinterpret_cast<const float *>(packs.slot[w]) + 2 * b + j) : -INFINITY;
         float m = row;
-        for (int w = 0; w < W; ++w) m = fmaxf(m, allp[(size_t)w * ld + 2 * b + j]);
+#pragma unroll
+        for (int w = 0; w < PEER_MAX; ++w) m = fmaxf(m, cp[w]);
         float sum = 0.f;
         if (m > -INFINITY) {
             sum = expf(row - m);
-            for (int w = 0; w < W; ++w) sum += expf(allp[(size_t)w * ld + 2 * b + j] - m);
+#pragma unroll
+            for (int w = 0; w < PEER_MAX; ++w)
+                if (w < W) sum += expf(cp[w] - m);
         }
         const float d = m + logf(sum);
         den[j] = d;
@@ -777,7 +827,8 @@ constexpr bool astat_enabled() { return B200_ASTAT != 0; }
 // fmt: tc::IDESC_A_BF16 / tc::IDESC_B_BF16 when that operand holds bfloat16 instead of float16.
 template <class Epi, bool A_MN = false, bool N_FAST = false, bool RANGE = false, bool B_MN = false>
 int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, int M, int N, int Kd,
-                 const typename Epi::Params &ep, cudaStream_t stream, const char *what, uint32_t fmt = 0) {
+                 const typename Epi::Params &ep, cudaStream_t stream, const char *what, uint32_t fmt = 0,
+                 int k_splits = 0) {
     CUtensorMap ma, mb;
     int rc = A_MN ? b200::make_tmap_2d_f16(&ma, A, (uint64_t)Kd, (uint64_t)M, (uint64_t)lda, 64)
                   : b200::make_tmap_2d_f16(&ma, A, (uint64_t)M, (uint64_t)Kd, (uint64_t)lda,
@@ -789,8 +840,9 @@ int launch_gemm2(const void *A, long long lda, const void *Bm, long long ldb, in
     if (rc) return rc;
     const int tiles = ((M + tc::PAIR_M - 1) / tc::PAIR_M) * ((N + tc::PAIR_N - 1) / tc::PAIR_N);
     const int max_pairs = num_sms() / 2;
-    const int pairs = tiles < max_pairs ? tiles : max_pairs;
-    tc::GemmShape shape{M, N, Kd, 0, 0, 0, fmt};
+    const int units = tiles * (k_splits > 1 ? k_splits : 1);
+    const int pairs = units < max_pairs ? units : max_pairs;
+    tc::GemmShape shape{M, N, Kd, 0, 0, 0, fmt, k_splits};
     (void)what;
     // short reductions with an epilogue-heavy functor: keep A resident, stream only B
     // (not for EpiG: its 32 KB store-staging buffer leaves only three ring stages next to the resident A and
@@ -1098,10 +1150,77 @@ int forward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfl
     return forward_shard_tail(p, row_lse, col_part, ws, st);
 }
 
+// Split-K for the sharded dvideo GEMM.  Its output has only (n/256) x (D/256) pair tiles - 32 at two ranks,
+// 8 at eight, against 74 CTA pairs - while the reduction runs over all B*K text rows, so without a split its time
+// does not go down with the rank count at all.  Slices: as many as keep one wave of (slice, tile) units within the
+// number of pairs, at least 8 k-blocks each, every slice non-empty, partial planes inside `cap_bytes` of scratch.
+int dvideo_splits(int n, int D, long long Kd, size_t cap_bytes) {
+    const int tiles = ((n + tc::PAIR_M - 1) / tc::PAIR_M) * ((D + tc::PAIR_N - 1) / tc::PAIR_N);
+    const int pairs = num_sms() / 2;
+    const int k_iters = (int)((Kd + tc::BLOCK_K - 1) / tc::BLOCK_K);
+    int s = pairs / std::max(tiles, 1);
+    s = std::min(s, k_iters / 8);
+    s = std::min<long long>(s, (long long)(cap_bytes / ((size_t)n * D * 4)));
+    if (s < 2) return 1;
+    const int kps = (k_iters + s - 1) / s;
+    s = (k_iters + kps - 1) / kps;      // drop slices the rounding left empty
+    return s < 2 ? 1 : s;
+}
+
+// out (rows x cols, float32 or bfloat16) = sum of `splits` float32 planes, added in slice order
+template <bool OUT_BF16>
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float4 *__restrict__ part, int splits, size_t count4, void *__restrict__ out) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < count4; g += stride) {
+        float4 a = part[g];
+        for (int k = 1; k < splits; ++k) {
+            const float4 b = part[(size_t)k * count4 + g];
+            a.x += b.x;
+            a.y += b.y;
+            a.z += b.z;
+            a.w += b.w;
+        }
+        if (OUT_BF16) {
+            __nv_bfloat162 h[2] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w)};
+            reinterpret_cast<uint2 *>(out)[g] = *reinterpret_cast<uint2 *>(h);
+        } else {
+            reinterpret_cast<float4 *>(out)[g] = a;
+        }
+    }
+}
+
+// dvideo (n, D) = G[own rows, :] . T of the rows-only scheme, with split-K when the rank's share is small
+int dvideo_shard(const Plan &p, const Operands &o, const __half *g, const float *grad_loss, void *dvideo, int grad_bf16,
+                 uint8_t *ws, cudaStream_t st) {
+    const size_t cap = p.n != p.B ? (size_t)p.B * p.ld_g2 * 2 : 0;   // the G2 region: unused by the rows-only scheme
+    const int splits = (p.D % 4 == 0) ? dvideo_splits(p.n, p.D, p.BK, cap) : 1;
+    const float alpha = 1.f / ((float)p.B * tc::G_SCALE);
+    if (splits <= 1) {
+        tc::EpiStore::Params sv{dvideo, (long long)p.D, alpha, grad_loss, o.s_text, grad_bf16};
+        return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, o.tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
+                                                                    "milnce dvideo GEMM (shard)");
+    }
+    float *part = reinterpret_cast<float *>(ws + p.off_gt);
+    tc::EpiStore::Params sv{part, (long long)p.D, alpha, grad_loss, o.s_text, 0, (long long)p.n * p.D};
+    int rc = launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, o.tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
+                                                                  "milnce dvideo GEMM (shard, split-K)", 0, splits);
+    if (rc) return rc;
+    const size_t count4 = (size_t)p.n * p.D / 4;
+    const int blocks = (int)std::min<size_t>((count4 + 255) / 256, (size_t)8 * num_sms());
+    if (grad_bf16)
+        splitk_reduce_kernel<true><<<blocks, 256, 0, st>>>(reinterpret_cast<const float4 *>(part), splits, count4, dvideo);
+    else
+        splitk_reduce_kernel<false><<<blocks, 256, 0, st>>>(reinterpret_cast<const float4 *>(part), splits, count4, dvideo);
+    b200::note_launches(1);
+    B200_LAUNCH_OK("milnce dvideo split-K reduce");
+    return 0;
+}
+
 int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bfloat16 *text,
                         const float *den, const float *nom, const float *grad_loss, void *dvideo,
                         int grad_bf16, void *dtext_partial, int dtext_bf16, int parts, int reuse, uint8_t *ws,
-                        cudaStream_t st) {
+                        cudaStream_t st, void *const *owner_dst = nullptr, int owners = 0) {
     // parts: 1 = G and the partial dtext, 2 = dvideo (from the G a parts-1 call left in the
     // workspace), 3 = both.  Split calls let the caller start the reduce-scatter of dtext
     // while dvideo is still being computed.
@@ -1110,11 +1229,7 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     const __half *vk = o.vk, *tk = o.tk;
     __half *g = reinterpret_cast<__half *>(ws + p.off_g);
     Scalars *sc = reinterpret_cast<Scalars *>(ws + p.off_scal);
-    if (parts == 2) {
-        tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
-        return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                       "milnce dvideo GEMM (shard)");
-    }
+    if (parts == 2) return dvideo_shard(p, o, g, grad_loss, dvideo, grad_bf16, ws, st);
     if (!reuse) {
         rc = stage_inputs<__nv_bfloat16>(p, video, text, ws, st, nullptr);
         if (rc) return rc;
@@ -1127,12 +1242,16 @@ int backward_shard_impl(const Plan &p, const __nv_bfloat16 *video, const __nv_bf
     if (rc) return rc;
     // partial dtext over the owned rows: (B*K, D) = G^T . V[own rows];  A = G read MN-major
     tc::EpiStore::Params sd{dtext_partial, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_video, dtext_bf16};
+    if (owner_dst) {
+        // the rows of the partial that rank q owns go straight to rank q's buffer (push over NVLink from the
+        // epilogue's stores): the reduce-scatter's transfer rides under this GEMM
+        sd.seg_rows = (int)(p.BK / owners);
+        for (int q = 0; q < 16; ++q) sd.seg[q] = owner_dst[q < owners ? q : 0];
+    }
     rc = launch_gemm2<tc::EpiStore, true, true, false, true>(g, p.ld_g, vk + (size_t)p.i0 * o.ld_vk, o.ld_vk, (int)p.BK, p.D, p.n, sd, st,
                                                 "milnce partial dtext GEMM (shard)");
     if (rc || parts == 1) return rc;
-    tc::EpiStore::Params sv{dvideo, (long long)p.D, 1.f / ((float)p.B * tc::G_SCALE), grad_loss, o.s_text, grad_bf16};
-    return launch_gemm2<tc::EpiStore, false, true, false, true>(g, p.ld_g, tk, o.ld_tk, p.n, p.D, (int)p.BK, sv, st,
-                                                   "milnce dvideo GEMM (shard)");
+    return dvideo_shard(p, o, g, grad_loss, dvideo, grad_bf16, ws, st);
 }
 
 int check_shard(const Plan &p, int dtype) {
@@ -1349,10 +1468,70 @@ extern "C" int milnce_forward_shard_peers(const void *const *slots, int W, int B
     PeerSlots ps;
     for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)slots[r < W ? r : 0];
     __half *vk = reinterpret_cast<__half *>(ws + p.off_vk), *tk = reinterpret_cast<__half *>(ws + p.off_tk);
-    stage_peers_kernel<<<4 * num_sms(), 256, 0, st>>>(ps, W, b, K, D, vk, tk, sc);   // ld_vk == ld_tk == D (D % 8 == 0)
+    stage_peers_kernel<<<4 * num_sms(), 256, 0, st>>>(ps, W, i0 / b, b, K, D, vk, tk, sc);   // ld_vk == ld_tk == D (D % 8 == 0)
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_forward_shard_peers staging");
     return forward_shard_tail(p, row_lse, col_part, ws, st);
+}
+
+extern "C" int milnce_backward_shard_push(const float *den, const float *nom, const float *grad_loss,
+                                          void *const *owner_dst, int W, int B, int K, int D, int i0, int n,
+                                          void *workspace, size_t workspace_bytes, void *stream) {
+    Plan p;
+    if (!make_plan(p, B, K, D, B200HEAD_BF16, i0, n)) {
+        b200::set_error("milnce_backward_shard_push: bad shape/range B=%d K=%d D=%d i0=%d n=%d", B, K, D, i0, n);
+        return B200HEAD_ERR_ARG;
+    }
+    if (!den || !nom || !grad_loss || !owner_dst || W < 1 || W > PEER_MAX || B % W != 0) {
+        b200::set_error("milnce_backward_shard_push: bad argument (1 <= W <= %d ranks, B a multiple of W)", PEER_MAX);
+        return B200HEAD_ERR_ARG;
+    }
+    if (((long long)(B / W) * K) % 128 != 0) {
+        b200::set_error("milnce_backward_shard_push: a rank's b*K text rows must be a multiple of 128");
+        return B200HEAD_ERR_ARG;
+    }
+    for (int q = 0; q < W; ++q)
+        if (!owner_dst[q] || (((uintptr_t)owner_dst[q]) & 15)) {
+            b200::set_error("milnce_backward_shard_push: destination %d is null or not 16-byte aligned", q);
+            return B200HEAD_ERR_ARG;
+        }
+    int rc = check_shard(p, B200HEAD_BF16);
+    if (rc) return rc;
+    rc = b200::check_device();
+    if (rc) return rc;
+    rc = check_common(p, workspace, workspace_bytes);
+    if (rc) return rc;
+    return backward_shard_impl(p, nullptr, nullptr, den, nom, grad_loss, nullptr, 0, nullptr, 1, /*parts=*/1,
+                               /*reuse=*/1, (uint8_t *)workspace, (cudaStream_t)stream, owner_dst, W);
+}
+
+extern "C" int milnce_peer_reduce_dtext(const void *const *partials, int W, int rank, int b, int K, int D,
+                                        void *dtext, int dtext_dtype, void *stream) {
+    if (!partials || !dtext || W < 1 || W > PEER_MAX || rank < 0 || rank >= W || b <= 0 || K <= 0 || D <= 0 ||
+        (dtext_dtype != B200HEAD_F32 && dtext_dtype != B200HEAD_BF16)) {
+        b200::set_error("milnce_peer_reduce_dtext: bad argument (1 <= W <= %d ranks, dtext_dtype F32 or BF16)", PEER_MAX);
+        return B200HEAD_ERR_ARG;
+    }
+    uintptr_t bits = (uintptr_t)dtext;
+    for (int r = 0; r < W; ++r) bits |= (uintptr_t)partials[r];
+    if (((size_t)b * K * D) % 8 != 0 || (bits & 15)) {
+        b200::set_error("milnce_peer_reduce_dtext: b*K*D must be a multiple of 8 and all pointers 16-byte aligned");
+        return B200HEAD_ERR_ARG;
+    }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    PeerSlots ps;
+    for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)partials[r < W ? r : 0];
+    const size_t count = (size_t)b * K * D / 8;
+    const int blocks = (int)std::min<size_t>((count + 255) / 256, (size_t)16 * num_sms());
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtext_dtype == B200HEAD_BF16)
+        peer_reduce_kernel<true><<<blocks, 256, 0, st>>>(ps, W, (size_t)rank * count, count, dtext);
+    else
+        peer_reduce_kernel<false><<<blocks, 256, 0, st>>>(ps, W, (size_t)rank * count, count, dtext);
+    b200::note_launches(1);
+    B200_LAUNCH_OK("milnce_peer_reduce_dtext");
+    return 0;
 }
 
 extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *den, float *nom,
@@ -1363,9 +1542,37 @@ extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *
     }
     int rc = b200::check_device();
     if (rc) return rc;
-    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(gathered, W, b, W * b, den, nom, loss);
+    if (W > PEER_MAX) {
+        b200::set_error("milnce_shard_combine: at most %d ranks", PEER_MAX);
+        return B200HEAD_ERR_ARG;
+    }
+    PeerSlots ps;
+    for (int r = 0; r < PEER_MAX; ++r)
+        ps.slot[r] = reinterpret_cast<const uint8_t *>(gathered + (size_t)(r < W ? r : 0) * ((size_t)2 * b + (size_t)W * b));
+    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(ps, W, b, W * b, den, nom, loss);
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_shard_combine");
+    return 0;
+}
+
+extern "C" int milnce_shard_combine_peers(const void *const *packs, int W, int b, float *den, float *nom, float *loss,
+                                          void *stream) {
+    if (!packs || !den || !nom || !loss || W <= 0 || W > PEER_MAX || b <= 0) {
+        b200::set_error("milnce_shard_combine_peers: bad argument (1 <= W <= %d ranks)", PEER_MAX);
+        return B200HEAD_ERR_ARG;
+    }
+    for (int r = 0; r < W; ++r)
+        if (!packs[r] || (((uintptr_t)packs[r]) & 3)) {
+            b200::set_error("milnce_shard_combine_peers: pack %d is null or misaligned", r);
+            return B200HEAD_ERR_ARG;
+        }
+    int rc = b200::check_device();
+    if (rc) return rc;
+    PeerSlots ps;
+    for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)packs[r < W ? r : 0];
+    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(ps, W, b, W * b, den, nom, loss);
+    b200::note_launches(1);
+    B200_LAUNCH_OK("milnce_shard_combine_peers");
     return 0;
 }
 

@@ -347,6 +347,7 @@ struct EpiCtx {
     int warp_slot;     // 0 .. 4*PARTS-1
     int sub, nsub;     // column sub-block of the tile this run covers, and how many a tile has (1 or 2)
     int dbg_tile;      // tile counter of this CTA (instrumented builds)
+    int slice;         // reduction slice of this work unit (GemmShape::k_splits), else 0
 };
 constexpr int SCRATCH_FLOATS = 2 * 4 * 128;
 // Every functor receives the finished fp32 accumulator (its row, its column half) in
@@ -365,6 +366,13 @@ struct EpiStore {
         const float *alpha_dev;      // optional device scalar multiplied into alpha
         const float *alpha_div_dev;  // optional device scalar alpha is divided by
         int out_bf16;
+        long long split_stride;      // elements between the output planes of consecutive reduction slices (0: none)
+        // Row-segmented output (0: off): rows [q * seg_rows, (q + 1) * seg_rows) are written to seg[q] (row index
+        // relative to the segment) instead of C.  seg_rows is a multiple of 128, so a CTA's rows share one
+        // segment.  The segments may be buffers in other GPUs' memory (peer-mapped): this is how the partial text
+        // gradient of the rows-only scheme is delivered to the ranks that own the rows, from the GEMM itself.
+        int seg_rows;
+        void *seg[16];
     };
     struct Tile {
         float alpha;
@@ -389,14 +397,21 @@ struct EpiStore {
     template <int HN>
     __device__ static void run(const Params &p, const EpiCtx &c, const Tile &t, float (&acc)[HN]) {
         const float alpha = t.alpha;
-        const int row = c.m0 + c.tid;
+        int row = c.m0 + c.tid;
         if (row >= c.M) return;
+        void *cbase = p.C;
+        if (p.seg_rows > 0) {
+            const int q = c.m0 / p.seg_rows;
+            cbase = p.seg[q];
+            row -= q * p.seg_rows;
+        }
 #pragma unroll
         for (int ch = 0; ch < HN / 32; ++ch) {
             const int col0 = c.n0 + ch * 32;
             if (col0 >= c.N) break;
             if (p.out_bf16) {
-                __nv_bfloat16 *dst = reinterpret_cast<__nv_bfloat16 *>(p.C) + (long long)row * p.ldc + col0;
+                __nv_bfloat16 *dst = reinterpret_cast<__nv_bfloat16 *>(cbase) + c.slice * p.split_stride +
+                                     (long long)row * p.ldc + col0;
                 if (col0 + 32 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
 #pragma unroll
                     for (int i = 0; i < 32; i += 8) {
@@ -414,7 +429,7 @@ struct EpiStore {
                 }
                 continue;
             }
-            float *dst = reinterpret_cast<float *>(p.C) + (long long)row * p.ldc + col0;
+            float *dst = reinterpret_cast<float *>(cbase) + c.slice * p.split_stride + (long long)row * p.ldc + col0;
             if (col0 + 32 <= c.N && ((((uintptr_t)dst) & 15) == 0)) {
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
@@ -906,6 +921,11 @@ struct GemmShape {
     // tensor core read both operands as bfloat16 instead of float16.  Both or neither: an instruction
     // with two different operand formats is rejected by the hardware (illegal instruction, measured).
     uint32_t idesc_or;
+    // CTA-pair streaming kernel: split the reduction into k_splits slices (0 or 1 = none).  A work unit is
+    // (slice, tile); the epilogue context carries the slice so that EpiStore can write each slice's partial
+    // result to its own plane (Params::split_stride), to be summed afterwards.  For GEMMs whose tile count is
+    // below the number of CTA pairs (the sharded dvideo: n/256 x D/256 tiles against a reduction of B*K).
+    int k_splits;
 };
 constexpr uint32_t IDESC_A_BF16 = 1u << 7, IDESC_B_BF16 = 1u << 10;
 
@@ -1087,6 +1107,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     } else {
         // ===================== epilogue warps 2..9 =====================
         EpiCtx c;
+        c.slice = 0;
         c.q = warp & 3;               // TMEM lane quarter this warp may access
         c.half = (warp - 2) >> 2;     // column half
         c.warp_slot = warp - 2;

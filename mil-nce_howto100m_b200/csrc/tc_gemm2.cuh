@@ -161,10 +161,14 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const int num_m = (shape.M + PAIR_M - 1) / PAIR_M;
     const int num_n = (shape.N + PAIR_N - 1) / PAIR_N;
     const int num_tiles = num_m * num_n;
-    const int k_iters = (shape.Kd + BLOCK_K - 1) / BLOCK_K;
+    const int k_iters_all = (shape.Kd + BLOCK_K - 1) / BLOCK_K;
+    // work units: (slice, tile), slice slowest; without split-K one slice covers the whole reduction
+    const int ksp = shape.k_splits > 1 ? shape.k_splits : 1;
+    const int kps = (k_iters_all + ksp - 1) / ksp;     // k-blocks per slice (the host keeps every slice non-empty)
+    const int num_units = num_tiles * ksp;
     static_assert(!RANGE || N_FAST, "contiguous ranges are defined on the n-fastest order");
-    const int t_begin = RANGE ? (int)((long long)pair * num_tiles / num_pairs) : pair;
-    const int t_end = RANGE ? (int)((long long)(pair + 1) * num_tiles / num_pairs) : num_tiles;
+    const int t_begin = RANGE ? (int)((long long)pair * num_units / num_pairs) : pair;
+    const int t_end = RANGE ? (int)((long long)(pair + 1) * num_units / num_pairs) : num_units;
     const int t_step = RANGE ? 1 : num_pairs;
 
     if (warp == 0 && lane == 0) {
@@ -194,12 +198,15 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = t_begin; t < t_end; t += t_step) {
+            for (int u = t_begin; u < t_end; u += t_step) {
+                const int slice = u / num_tiles;
+                const int t = u - slice * num_tiles;
                 const int m_blk = N_FAST ? t / num_n : t % num_m;
                 const int n_blk = N_FAST ? t % num_n : t / num_m;
                 const int m0 = m_blk * PAIR_M + (int)rank * BLOCK_M;        // my rows of A
                 const int n0 = n_blk * PAIR_N + (int)rank * (PAIR_N / 2);   // my half of B
-                for (int kb = 0; kb < k_iters; ++kb) {
+                const int kb_end = min(k_iters_all, (slice + 1) * kps);
+                for (int kb = slice * kps; kb < kb_end; ++kb) {
                     mbar_wait_warp(&empty_bar[stage], phase ^ 1);
                     if (elect_one()) {
                         const uint32_t lead_full = mapa_u32(smem_u32(&full_bar[stage]), 0);
@@ -245,6 +252,8 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 tcgen05_fence_after();
                 epi_stamp(Epi::STAMP_KIND, (int)cc, 1);
                 const uint32_t tmem_d = tmem_base + buf * PAIR_N;
+                const int slice_k0 = (t / num_tiles) * kps;
+                const int k_iters = min(k_iters_all, slice_k0 + kps) - slice_k0;
                 for (int kb = 0; kb < k_iters; ++kb) {
                     mbar_wait_warp(&full_bar[stage], phase);
                     tcgen05_fence_after();
@@ -288,14 +297,20 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         // tile coordinates advance incrementally (no integer division per tile): (fast, slow) are
         // (n, m) in n-fastest order and (m, n) otherwise
         const int fast_n = N_FAST ? num_n : num_m;
-        int cur_fast = t_begin % fast_n, cur_slow = t_begin / fast_n;
-        const int step_fast = t_step % fast_n, step_slow = t_step / fast_n;
+        const int slow_n = N_FAST ? num_m : num_n;
+        int cur_fast = t_begin % fast_n, cur_slow = (t_begin / fast_n) % slow_n, cur_slice = t_begin / num_tiles;
+        const int step_fast = t_step % fast_n, step_slow = (t_step / fast_n) % slow_n, step_slice = t_step / num_tiles;
         auto advance = [&](int &f, int &sl) {
             f += step_fast;
             sl += step_slow;
+            cur_slice += step_slice;
             if (f >= fast_n) {
                 f -= fast_n;
                 ++sl;
+            }
+            if (sl >= slow_n) {
+                sl -= slow_n;
+                ++cur_slice;
             }
         };
         // per-sample values of a tile are loaded one tile ahead (Epi::preload), see EpiG
@@ -311,6 +326,7 @@ gemm_tn_2cta_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             const int prev_m0 = c.m0;
             c.m_blk = (N_FAST ? cur_slow : cur_fast) * 2 + (int)rank;   // 128-row block index of this CTA's rows
             c.m0 = c.m_blk * BLOCK_M;
+            c.slice = cur_slice;
             advance(cur_fast, cur_slow);  // now the coordinates of the next tile of this pair
             const uint32_t buf = cc & 1;
             c.dbg_tile = (int)cc;
@@ -541,6 +557,7 @@ gemm_tn_2cta_astat_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
     } else {
         // ===================== epilogue warps (both CTAs) =====================
         EpiCtx c;
+        c.slice = 0;
         c.q = warp & 3;
         c.half = (warp - 2) >> 2;
         c.warp_slot = warp - 2;

@@ -116,7 +116,7 @@ class CudaBackend:
         dev = video_local.device
         nbytes = lib.milnce_workspace_bytes(B, K, D, _lib.BF16, b)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        pack = torch.empty(2 * b + B, dtype=torch.float32, device=dev)
+        pack = ring.pack        # this rank's statistics, where the peers can read them
         slot_ptr, peer_ptrs = ring.next_slot()
         with torch.cuda.device(dev):
             st = _lib.stream_ptr(dev)
@@ -129,6 +129,58 @@ class CudaBackend:
                                                 ctypes.c_void_p(pack.data_ptr() + 8 * b), _ptr(ws), nbytes, st)
             _lib.check(rc, "milnce_forward_shard_peers")
         return pack, ws
+
+    @staticmethod
+    def backward_shard_push(ring, den, nom, grad_loss, world, rank, ws):
+        """Gradient tiles + partial text gradient, each owner's rows written straight into that rank's receive
+        area in peer-mapped memory (include/b200head.h, milnce_backward_shard_push)."""
+        lib = _lib.load()
+        b, K, D = ring.shape
+        dev = ring.grad.device
+        block = b * K * D * 2        # bytes of one (b*K, D) bf16 block; my block in q's area is block number `rank`
+        arr = (ctypes.c_void_p * world)(*[p + rank * block for p in ring.grad_ptrs])
+        with torch.cuda.device(dev):
+            rc = lib.milnce_backward_shard_push(_ptr(den), _ptr(nom), _ptr(grad_loss), arr, world, world * b, K, D,
+                                                rank * b, b, _ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_backward_shard_push")
+
+    @staticmethod
+    def peer_reduce_dtext(ring, world, rank, out_dtype, pushed=False, out=None):
+        """This rank's (b*K, D) text gradient.  pushed=False: the sum of its block of every rank's partial, read
+        from the peers' memory; pushed=True: the sum of the W blocks the peers delivered into this rank's own
+        receive area (include/b200head.h, milnce_peer_reduce_dtext).  The caller has passed ring.barrier()."""
+        lib = _lib.load()
+        b, K, D = ring.shape
+        dev = ring.grad.device
+        dt = out if out is not None else torch.empty(b * K, D, dtype=out_dtype, device=dev)
+        if pushed:
+            mine = ring.grad_ptrs[rank]
+            arr = (ctypes.c_void_p * world)(*[mine + q * b * K * D * 2 for q in range(world)])
+            rank = 0
+        else:
+            arr = (ctypes.c_void_p * world)(*ring.grad_ptrs)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_peer_reduce_dtext(arr, world, rank, b, K, D, _ptr(dt),
+                                              0 if out_dtype == torch.float32 else 1, _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_peer_reduce_dtext")
+        return dt
+
+    @staticmethod
+    def shard_combine_peers(ring, world):
+        """(den[B], nom[B], loss) from the W statistics packs in the ranks' peer-readable memory; the caller has
+        passed ring.barrier() after forward_shard_peers."""
+        lib = _lib.load()
+        b = ring.shape[0]
+        dev = ring.pack.device
+        B = world * b
+        den = torch.empty(B, dtype=torch.float32, device=dev)
+        nom = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        arr = (ctypes.c_void_p * world)(*ring.pack_ptrs)
+        with torch.cuda.device(dev):
+            rc = lib.milnce_shard_combine_peers(arr, world, b, _ptr(den), _ptr(nom), _ptr(loss), _lib.stream_ptr(dev))
+        _lib.check(rc, "milnce_shard_combine_peers")
+        return den, nom, loss.reshape(())
 
     @staticmethod
     def shard_combine(gathered, world, b):
@@ -147,11 +199,12 @@ class CudaBackend:
 
     @staticmethod
     def backward_shard(video, text, den, nom, grad_loss, i0, n, ws, parts=3, grad_dtype=torch.float32,
-                       partial_dtype=torch.float32, dims=None):
+                       partial_dtype=torch.float32, dims=None, partial_out=None):
         """Returns (dvideo (n, D) in grad_dtype or None, dtext_partial (B*K, D) in partial_dtype or None).
 
         parts=1: gradient tiles + dtext_partial only; parts=2: dvideo only, from the workspace a
-        parts=1 call left; parts=3: both.  dtext_partial is to be reduce-scattered."""
+        parts=1 call left; parts=3: both.  dtext_partial is to be reduce-scattered (NCCL, or
+        peer_reduce_dtext when `partial_out` is a buffer the peers can read)."""
         lib = _lib.load()
         if dims is not None:        # (B, K, D) given explicitly: video / text are then only the local shards
             B, K, D = dims          # and are not read (the workspace of the forward holds the operands)
@@ -170,7 +223,14 @@ class CudaBackend:
             ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
             reuse = 0
         dv = torch.empty(n, D, dtype=grad_dtype, device=dev) if parts & 2 else None
-        dtp = torch.empty(B * K, D, dtype=partial_dtype, device=dev) if parts & 1 else None
+        dtp = None
+        if parts & 1:
+            if partial_out is not None:
+                if partial_out.dtype != partial_dtype or partial_out.numel() != B * K * D:
+                    raise ValueError("partial_out must hold (B*K, D) values of partial_dtype")
+                dtp = partial_out.view(B * K, D)
+            else:
+                dtp = torch.empty(B * K, D, dtype=partial_dtype, device=dev)
         gcode = 0 if grad_dtype == torch.float32 else 1
         pcode = 0 if partial_dtype == torch.float32 else 1
         null = ctypes.c_void_p(0)

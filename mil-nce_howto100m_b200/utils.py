@@ -82,18 +82,34 @@ class PeerRing:
     all shards straight from the peers' slots over NVLink (milnce_forward_shard_peers).  One slot, two
     barriers per step: the first keeps a fast rank from overwriting a slot that a slow peer is still
     reading from the previous step, the second says that every slot is complete.  (Barriers are kernels on
-    the current stream, so the sequence can be captured in a CUDA graph.)"""
+    the current stream, so the sequence can be captured in a CUDA graph.)
+
+    The same allocation holds this rank's partial text gradient: backward writes it there, a third barrier
+    follows, and every rank sums its own block of all partials from the peers' memory
+    (milnce_peer_reduce_dtext) - the reduce-scatter without a collective kernel competing for SMs with the
+    dvideo GEMM.  The next step's two forward barriers keep it from being overwritten while a peer still reads."""
 
     def __init__(self, b, K, D, device, group=None):
         import torch.distributed._symmetric_memory as symm_mem
         from . import _lib
         lib = _lib.load()
         self.slot_bytes = int(lib.milnce_peer_slot_bytes(b, K, D))
-        self.buf = symm_mem.empty(self.slot_bytes, dtype=torch.uint8, device=device)
-        self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        pg = group if group is not None else dist.group.WORLD
+        world = dist.get_world_size(pg)
+        # one allocation: [slot | (B*K, D) bfloat16 partial text gradient of this rank | its statistics pack]
+        grad_bytes = world * b * K * D * 2
+        pack_off = self.slot_bytes + (grad_bytes + 255) // 256 * 256
+        pack_bytes = (2 * b + world * b) * 4
+        self.buf = symm_mem.empty(pack_off + pack_bytes, dtype=torch.uint8, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, pg)
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.grad_ptrs = [p + self.slot_bytes for p in self.ptrs]
+        self.grad = self.buf[self.slot_bytes:self.slot_bytes + grad_bytes].view(torch.bfloat16)
+        self.pack_ptrs = [p + pack_off for p in self.ptrs]
+        self.pack = self.buf[pack_off:pack_off + pack_bytes].view(torch.float32)
         self.rank = int(self.hdl.rank)
         self.shape = (b, K, D)
+        self.side = torch.cuda.Stream(device=device)     # barrier + gradient reduction run here, beside dvideo
 
     def next_slot(self):
         self.hdl.barrier(channel=0)          # nobody is still reading the slots of the previous step
@@ -182,27 +198,35 @@ class _GatheredMILNCERows(torch.autograd.Function):
             pack, ws = backend.forward_shard_peers(ring, v, t, world, rank)
             V, T = v, t                      # (only their shapes are used from here on)
             _mark(marks, "publish+stage+forward_kernels", v.device)
+            if opts.get("reduce") != "nccl":
+                # the statistics stay where they are: barrier, then every rank reads all W packs
+                ring.barrier()
+                _mark(marks, "stats_exchange", v.device)
+                den, nom_all, loss = backend.shard_combine_peers(ring, world)
+                _mark(marks, "combine", v.device)
+                pack = None
         else:
             V, T = _gather_embeddings(v, t, world, group)
             _mark(marks, "gather_embeddings", v.device)
             # the kernels write [row_lse of my samples | nom of my samples | my column partials] in place
             pack, ws = backend.forward_shard(V, T, i0, b)
             _mark(marks, "forward_kernels", v.device)
-        allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
-        dist.all_gather_into_tensor(allp, pack, group=group)
-        _mark(marks, "stats_exchange", v.device)
-        den, nom_all, loss = backend.shard_combine(allp.view(world, 2 * b + B), world, b)
-        _mark(marks, "combine", v.device)
+        if pack is not None:
+            allp = torch.empty(world * pack.numel(), dtype=pack.dtype, device=pack.device)
+            dist.all_gather_into_tensor(allp, pack, group=group)
+            _mark(marks, "stats_exchange", v.device)
+            den, nom_all, loss = backend.shard_combine(allp.view(world, 2 * b + B), world, b)
+            _mark(marks, "combine", v.device)
         ctx.save_for_backward(V, T, den, nom_all)
         ctx.ws = ws
         ctx.meta = (i0, b, backend, v.dtype, t.dtype, group, t.shape[0], marks, opts.get("partial_dtype"),
-                    (B, t.shape[0] // b, v.shape[1]))
+                    (B, t.shape[0] // b, v.shape[1]), ring, opts.get("reduce"))
         return loss
 
     @staticmethod
     def backward(ctx, grad_output):
         V, T, den, nom = ctx.saved_tensors
-        i0, b, backend, vdt, tdt, group, bk_local, marks, pdt, dims = ctx.meta
+        i0, b, backend, vdt, tdt, group, bk_local, marks, pdt, dims, ring, reduce = ctx.meta
         _mark(marks, "backward_start", V.device)
         g = grad_output.detach().reshape(1).to(torch.float32).contiguous()
         # default: partials in the embeddings' own 16-bit dtype - the result is rounded to that dtype anyway, and
@@ -210,6 +234,30 @@ class _GatheredMILNCERows(torch.autograd.Function):
         # (profiles/r2_multi_timeline_*.txt); float32 on request (partial_dtype=torch.float32)
         pdt = pdt if pdt is not None else (torch.bfloat16 if tdt == torch.bfloat16 else torch.float32)
         # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
+        if ring is not None and pdt == torch.bfloat16 and reduce != "nccl":
+            world, rank = dims[0] // b, i0 // b
+            push = reduce == "push" and (b * dims[1]) % 128 == 0
+            if push:
+                # the dtext GEMM's epilogue stores every owner's rows into that rank's memory
+                backend.backward_shard_push(ring, den, nom, g, world, rank, ctx.ws)
+            else:
+                # partial into my own peer-readable buffer; every rank later reads its block of all partials
+                backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt, dims=dims,
+                                       partial_out=ring.grad)
+            _mark(marks, "gradient_tiles+dtext_partial", V.device)
+            # barrier + reduction on a side stream, next to the dvideo GEMM (whose split-K units leave SMs free)
+            main = torch.cuda.current_stream(V.device)
+            dt = torch.empty(dims[1] * b, dims[2], dtype=tdt, device=V.device)
+            ring.side.wait_stream(main)
+            with torch.cuda.stream(ring.side):
+                ring.barrier()
+                backend.peer_reduce_dtext(ring, world, rank, tdt, pushed=push, out=dt)
+            dv, _ = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=2, grad_dtype=vdt, dims=dims)
+            ctx.ws = None
+            _mark(marks, "dvideo", V.device)
+            main.wait_stream(ring.side)
+            _mark(marks, "peer_reduce_dtext", V.device)
+            return dv, dt, None, None, None, None, None
         _, dt_partial = backend.backward_shard(V, T, den, nom, g, i0, b, ctx.ws, parts=1, partial_dtype=pdt, dims=dims)
         _mark(marks, "gradient_tiles+dtext_partial", V.device)
         dt = torch.empty((bk_local, dt_partial.shape[1]), dtype=dt_partial.dtype, device=dt_partial.device)
@@ -231,7 +279,8 @@ class GatheredMILNCELoss(torch.nn.Module):
     embeddings of this rank.
     """
 
-    def __init__(self, args=None, group=None, scheme="auto", partial_dtype=None, gather="auto", _backend=None):
+    def __init__(self, args=None, group=None, scheme="auto", partial_dtype=None, gather="auto", reduce="auto",
+                 _backend=None):
         """scheme: "rows" (each rank computes only its rows of S, reduce-scatter of the text
         gradient; bf16 embeddings), "rowcol" (row block + column block per rank, no gradient
         collective - the reference's communication pattern), or "auto" (rows when available).
@@ -241,8 +290,16 @@ class GatheredMILNCELoss(torch.nn.Module):
         "peer" (no collective: shards are read from the peers' memory, see PeerRing; needs CUDA bf16
         embeddings, a local batch that is a multiple of 64, D a multiple of 8, at most 16 ranks), or
         "auto" (peer when those conditions hold and symmetric memory can be set up, else nccl).
+        reduce: the gradient collective of the rows scheme on the peer path - "pull" / "auto" (bfloat16 partials
+        stay in the rank's peer-readable buffer and every rank sums its block of all W partials, beside the
+        dvideo GEMM), "push" (the text-gradient GEMM's epilogue stores each owner's rows into that rank's
+        memory; measured slower: 16-byte stores over NVLink stall the epilogue), or "nccl" (reduce-scatter; also
+        keeps the statistics all-gather on NCCL).
         _backend: private test seam (the CPU tests drive the orchestration with a stand-in)."""
         super().__init__()
+        if reduce not in ("auto", "nccl", "pull", "push"):
+            raise ValueError("reduce must be 'auto', 'nccl', 'pull' or 'push'")
+        self.reduce = reduce
         if scheme not in ("auto", "rows", "rowcol"):
             raise ValueError("scheme must be 'auto', 'rows' or 'rowcol'")
         if gather not in ("auto", "nccl", "peer"):
@@ -277,7 +334,7 @@ class GatheredMILNCELoss(torch.nn.Module):
         fn = _GatheredMILNCERows if use_rows else _GatheredMILNCE
         ring = self._peer_ring(video_embd, text_embd, world) if (use_rows and self._backend is None) else None
         self.last_gather = "peer" if ring is not None else ("nccl" if world > 1 else None)
-        opts = {"marks": self._marks, "partial_dtype": self.partial_dtype, "ring": ring}
+        opts = {"marks": self._marks, "partial_dtype": self.partial_dtype, "ring": ring, "reduce": self.reduce}
         return fn.apply(video_embd, text_embd, world, rank, self.group, backend, opts)
 
 
@@ -327,11 +384,12 @@ class GraphedGatheredMILNCEStep:
     """
 
     def __init__(self, b, K, D, dtype=torch.bfloat16, device=None, group=None, scheme="auto",
-                 partial_dtype=None, gather="auto", warmup=3):
+                 partial_dtype=None, gather="auto", reduce="auto", warmup=3):
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.video = torch.zeros(b, D, dtype=dtype, device=dev).requires_grad_(True)
         self.text = torch.zeros(b * K, D, dtype=dtype, device=dev).requires_grad_(True)
-        self.module = GatheredMILNCELoss(group=group, scheme=scheme, partial_dtype=partial_dtype, gather=gather)
+        self.module = GatheredMILNCELoss(group=group, scheme=scheme, partial_dtype=partial_dtype, gather=gather,
+                                         reduce=reduce)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):       # warm-up off the capture: communicators, library, allocator

@@ -48,7 +48,12 @@ def main():
 
     variants = [("rows/f32-partial", dict(scheme="rows", partial_dtype=torch.float32, gather="nccl")),
                 ("rows/bf16-partial", dict(scheme="rows", partial_dtype=torch.bfloat16, gather="nccl")),
-                ("rows/bf16-partial/peer-memory gather", dict(scheme="rows", partial_dtype=torch.bfloat16, gather="peer")),
+                ("rows/bf16-partial/peer-memory gather, nccl reduce-scatter",
+                 dict(scheme="rows", partial_dtype=torch.bfloat16, gather="peer", reduce="nccl")),
+                ("rows/bf16-partial/peer-memory gather, pull reduce from peer memory",
+                 dict(scheme="rows", partial_dtype=torch.bfloat16, gather="peer", reduce="pull")),
+                ("rows/bf16-partial/peer-memory gather, push from the dtext GEMM epilogue",
+                 dict(scheme="rows", partial_dtype=torch.bfloat16, gather="peer", reduce="push")),
                 ("rowcol", dict(scheme="rowcol"))]
     if args.only:
         variants = [v for v in variants if args.only in v[0]]

@@ -207,7 +207,9 @@ def test_rows_only_sharding_emulated_on_one_gpu():
             dvr, none = CudaBackend.backward_shard(v, t, den_all, nom_all, one, r * b, b, o[1], parts=2,
                                                    grad_dtype=torch.bfloat16)
             assert none is None and dvr.dtype == torch.bfloat16
-        tol = 5e-6 if dvr.dtype == torch.float32 else 3e-3  # bf16 output: 2^-9 rounding per element
+        # float32 output: the sharded dvideo GEMM splits its reduction into slices (a different summation order and
+        # shorter tensor-core accumulation chains than the single-GPU GEMM); bf16 output: 2^-9 rounding per element
+        tol = 5e-5 if dvr.dtype == torch.float32 else 3e-3
         assert rel_err(dvr.float().cpu().numpy(), dv[r * b:(r + 1) * b].cpu().numpy()) < tol
         dt_sum += dtp
     assert rel_err(dt_sum.cpu().numpy(), dt.cpu().numpy()) < 5e-6

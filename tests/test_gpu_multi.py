@@ -25,7 +25,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, scheme, out, gather="nccl"):
+def _worker(rank, world, port, scheme, out, gather="nccl", reduce="auto"):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -40,7 +40,7 @@ def _worker(rank, world, port, scheme, out, gather="nccl"):
         T = (torch.randn(B * K, D, generator=g) * 0.1).bfloat16().cuda()
         v_loc = V[rank * b:(rank + 1) * b].clone().requires_grad_(True)
         t_loc = T[rank * b * K:(rank + 1) * b * K].clone().requires_grad_(True)
-        mod = milnce_b200.GatheredMILNCELoss(scheme=scheme, gather=gather)
+        mod = milnce_b200.GatheredMILNCELoss(scheme=scheme, gather=gather, reduce=reduce)
         loss = mod(v_loc, t_loc)
         loss.backward()
         if gather == "peer":
@@ -127,12 +127,16 @@ def test_graphed_gathered_step_two_gpus_nccl():
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 @pytest.mark.timeout(240)
-def test_gathered_loss_peer_memory_two_gpus():
+@pytest.mark.parametrize("reduce", ["pull", "push", "nccl"])
+def test_gathered_loss_peer_memory_two_gpus(reduce):
     """gather="peer": no embedding all-gather; the shards are published in symmetric memory and staged from the
-    peers' buffers (milnce_peer_publish / milnce_forward_shard_peers)."""
+    peers' buffers (milnce_peer_publish / milnce_forward_shard_peers).  reduce="push": the text-gradient GEMM
+    delivers each owner's rows into that rank's memory (milnce_backward_shard_push) and every rank sums what it
+    received (milnce_peer_reduce_dtext); "pull": partials stay local and are read from the peers; "nccl":
+    reduce-scatter."""
     world = 2
     out = mp.get_context("spawn").Array("i", [0] * world)
-    mp.spawn(_worker, args=(world, _free_port(), "rows", out, "peer"), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), "rows", out, "peer", reduce), nprocs=world, join=True)
     assert list(out) == [1] * world
 
 
