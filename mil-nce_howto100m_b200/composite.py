@@ -66,6 +66,31 @@ class SDTW_CIDM(torch.nn.Module):
         return torch.mean(I_x + I_y + dtw)
 
 
+class SDTW_negative(torch.nn.Module):
+    """reference loss.py:70-91: soft-DTW of the matching pairs plus, per video sequence, the sum of
+    exp(<frame, word>) over all its frames and ALL text frames - with the entries against its own text
+    sequence set to 0 before the exp (so each contributes exp(0) = 1, as in the reference, :84) - over b - 1.
+
+    The reference hard-codes b = 160 sequences of L = 8 frames and d = 512 (chunk(160), the 1288 * i + j mask,
+    view(160, 8), / 159); here b, L and d come from the inputs, which is the same computation at that size.
+    The chunk / cat / mask / chunk / cat shuffle of :81-86 is a (b, L, b, L) view with its diagonal blocks zeroed."""
+
+    def __init__(self, args):
+        super().__init__()
+        self.args = args
+        self.sdtw = SoftDTW(use_cuda=True, gamma=1e-1, dist_func="cosine")
+        self.device = self.args.rank
+
+    def forward(self, video_embd, text_embd):
+        b, L, d = video_embd.shape
+        sdtw_loss = self.sdtw(video_embd, text_embd)
+        pairwise = torch.matmul(video_embd.reshape(-1, d), text_embd.reshape(-1, d).t()).view(b, L, b, -1)
+        own = torch.eye(b, dtype=torch.bool, device=pairwise.device).view(b, 1, b, 1)
+        pairwise = pairwise.masked_fill(own, 0.)
+        negative_loss = torch.exp(pairwise).sum(dim=(1, 2, 3))
+        return torch.mean(sdtw_loss + negative_loss / (b - 1))
+
+
 class SDTW_3(torch.nn.Module):
     """reference loss.py:93-134: three contrastive terms, each over all b*b sequence pairs."""
 

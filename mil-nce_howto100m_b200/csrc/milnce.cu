@@ -740,29 +740,62 @@ shard_combine_kernel(PeerSlots packs, int W, int b, int B, float *__restrict__ d
                      float *__restrict__ nom_all, float *__restrict__ loss) {
     __shared__ double sh[32];
     double acc = 0.0;
-    for (int j = threadIdx.x; j < B; j += blockDim.x) {
-        const int r = j / b, i = j - r * b;
-        const float *own = reinterpret_cast<const float *>(packs.slot[r]);
-        const float row = __ldcg(own + i);
-        const float nm = __ldcg(own + b + i);
-        float cp[PEER_MAX];
+    // four samples per thread and round: all their loads (2 + W each, possibly from other GPUs' memory) are in
+    // flight together - one sample at a time cost a remote round trip per sample (31 us at B = 8192, W = 2)
+    constexpr int J = 4;
+    for (int j0 = threadIdx.x; j0 < B; j0 += J * blockDim.x) {
+        float row[J], nm[J], m[J], sum[J];
 #pragma unroll
-        for (int w = 0; w < PEER_MAX; ++w)
-            cp[w] = w < W ? __ldcg(reinterpret_cast<const float *>(packs.slot[w]) + 2 * b + j) : -INFINITY;
-        float m = row;
-#pragma unroll
-        for (int w = 0; w < PEER_MAX; ++w) m = fmaxf(m, cp[w]);
-        float sum = 0.f;
-        if (m > -INFINITY) {
-            sum = expf(row - m);
-#pragma unroll
-            for (int w = 0; w < PEER_MAX; ++w)
-                if (w < W) sum += expf(cp[w] - m);
+        for (int u = 0; u < J; ++u) {
+            const int j = j0 + u * blockDim.x;
+            row[u] = nm[u] = -INFINITY;
+            if (j < B) {
+                const int r = j / b, i = j - r * b;
+                const float *own = reinterpret_cast<const float *>(packs.slot[r]);
+                row[u] = __ldcg(own + i);
+                nm[u] = __ldcg(own + b + i);
+            }
+            m[u] = row[u];
+            sum[u] = 0.f;
         }
-        const float d = m + logf(sum);
-        den[j] = d;
-        nom_all[j] = nm;
-        acc += (double)(d - nm);
+        // column partials: running (max, sum) pairs, W loads per sample issued back to back
+        for (int w0 = 0; w0 < W; w0 += 4) {
+            float cp[J][4];
+#pragma unroll
+            for (int u = 0; u < J; ++u) {
+                const int j = j0 + u * blockDim.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    cp[u][k] = (j < B && w0 + k < W)
+                                   ? __ldcg(reinterpret_cast<const float *>(packs.slot[w0 + k]) + 2 * b + j)
+                                   : -INFINITY;
+            }
+#pragma unroll
+            for (int u = 0; u < J; ++u) {
+                float mx = m[u];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) mx = fmaxf(mx, cp[u][k]);
+                if (mx > -INFINITY) {
+                    float sacc = sum[u] * expf(m[u] - mx);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) sacc += expf(cp[u][k] - mx);   // exp(-inf) = 0 for the padding
+                    sum[u] = sacc;
+                    m[u] = mx;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < J; ++u) {
+            const int j = j0 + u * blockDim.x;
+            if (j >= B) continue;
+            // the row statistic joins last: den = logaddexp(row, logsumexp_r col_part[r])
+            float s_all = sum[u], mm = m[u];
+            if (mm > -INFINITY) s_all += expf(row[u] - mm);
+            const float d = mm > -INFINITY ? mm + logf(s_all) : -INFINITY;
+            den[j] = d;
+            nom_all[j] = nm[u];
+            acc += (double)(d - nm[u]);
+        }
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;

@@ -122,7 +122,7 @@ def golden_sdtw(ref_sdtw):
 
 
 def golden_composite(ref_loss, ref_sdtw):
-    """The composite soft-DTW losses of reference loss.py:20-134 (CDTW, SDTW_CIDM, SDTW_3), executed with
+    """The composite soft-DTW losses of reference loss.py:20-134 (CDTW, SDTW_CIDM, SDTW_negative, SDTW_3), executed with
     the one deviation the docstring above names: every ``SoftDTW(use_cuda=True, ...)`` they construct is
     built with ``use_cuda=False`` (numba-CPU path); their own code is not touched."""
     class Args:
@@ -166,9 +166,20 @@ def golden_composite(ref_loss, ref_sdtw):
         out.backward()
         rec.update(cidm_video=v32.numpy(), cidm_text=t32.numpy(), cidm_start=start.numpy(), cidm_end=end.numpy(),
                    cidm_out=np.float64(out.item()), cidm_dvideo=v.grad.numpy(), cidm_dtext=t.grad.numpy())
+        # SDTW_negative: the reference hard-codes 160 sequences of 8 frames, d = 512 (:80-88), so the fixture
+        # has that size; inputs are multiples of 1/32 stored as int8, gradients kept for two sequences only
+        vi = torch.randint(-8, 9, (160, 8, 512), generator=g, dtype=torch.int8)
+        ti = torch.randint(-8, 9, (160, 8, 512), generator=g, dtype=torch.int8)
+        v = (vi.double() / 32).requires_grad_(True)
+        t = (ti.double() / 32).requires_grad_(True)
+        out = ref_loss.SDTW_negative(Args())(v, t)
+        out.backward()
+        rec.update(neg_video_i8=vi.numpy(), neg_text_i8=ti.numpy(), neg_out=np.float64(out.item()),
+                   neg_dvideo_first2=v.grad[:2].numpy(), neg_dtext_first2=t.grad[:2].numpy(),
+                   neg_dvideo_norm=np.float64(v.grad.norm().item()), neg_dtext_norm=np.float64(t.grad.norm().item()))
         np.savez_compressed(os.path.join(OUT, "composite_losses.npz"), **rec)
         print(f"composite_losses: {len(rec)} arrays; CDTW {rec['cdtw_out']}, SDTW_3 {rec['s3_losses']}, "
-              f"SDTW_CIDM {rec['cidm_out']}")
+              f"SDTW_CIDM {rec['cidm_out']}, SDTW_negative {rec['neg_out']}")
     finally:
         ref_loss.SoftDTW = real
 

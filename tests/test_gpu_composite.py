@@ -107,6 +107,21 @@ def test_sdtw_cidm_matches_executed_reference():
     assert rel_err(t.grad.cpu().numpy(), f["cidm_dtext"]) < 1e-4
 
 
+def test_sdtw_negative_matches_executed_reference():
+    """At the size the reference hard-codes (160 sequences x 8 frames x 512, loss.py:80-88)."""
+    f = _fix()
+    v = (torch.from_numpy(f["neg_video_i8"]).float() / 32).cuda().requires_grad_(True)
+    t = (torch.from_numpy(f["neg_text_i8"]).float() / 32).cuda().requires_grad_(True)
+    out = milnce_b200.SDTW_negative(Args())(v, t)
+    out.backward()
+    torch.cuda.synchronize()
+    assert abs(out.item() - float(f["neg_out"])) < 1e-5 * abs(float(f["neg_out"]))
+    assert rel_err(v.grad[:2].cpu().numpy(), f["neg_dvideo_first2"]) < 1e-4
+    assert rel_err(t.grad[:2].cpu().numpy(), f["neg_dtext_first2"]) < 1e-4
+    assert abs(v.grad.double().norm().item() - float(f["neg_dvideo_norm"])) < 1e-4 * float(f["neg_dvideo_norm"])
+    assert abs(t.grad.double().norm().item() - float(f["neg_dtext_norm"])) < 1e-4 * float(f["neg_dtext_norm"])
+
+
 def test_normalize_reads_operands_in_place():
     """normalize=True without the reference's cat([X, X, Y]) / cat([Y, X, Y]) copies: same value and
     gradients as the stacked formulation evaluated through this package."""
