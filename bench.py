@@ -73,6 +73,36 @@ def peaks():
     return {"hbm": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "src": "B200_PROFILING.md fallback"}
 
 
+def measure_tf32_peak(dev, seconds=0.4):
+    """cuBLAS TF32 GEMM throughput (TFLOP/s), measured here the way MEASURED_PEAKS.json measures bf16: an
+    8192^3 torch.matmul with allow_tf32, CUDA events, after warm-up.  Only for --dtype fp32, whose operands are
+    float32 (BASELINE.md section 2 asks for the roofline of that mode against a TF32 peak)."""
+    n = 8192
+    a = torch.randn(n, n, device=dev)
+    b = torch.randn(n, n, device=dev)
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        for _ in range(3):
+            torch.matmul(a, b)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps, best = 10, 0.0
+        elapsed = 0.0
+        while elapsed < seconds:
+            e0.record()
+            for _ in range(reps):
+                torch.matmul(a, b)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            t = e0.elapsed_time(e1) / 1e3
+            elapsed += t
+            best = max(best, 2.0 * n ** 3 * reps / t / 1e12)
+        return best
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -498,7 +528,13 @@ def run_b200(args):
                               f"power cap {'seen' if capped else 'not seen'}); traffic = DRAM bytes of one step "
                               f"(ncu --set full, {traffic.get('_file')})")},
     }
-    if sustained is not None:
+    if args.dtype == "fp32":
+        tf32 = measure_tf32_peak(dev) if rank == 0 or world > 1 else 0.0
+        line["roofline"].update({"peak": tf32 * world, "frac": achieved / (tf32 * world),
+                                 "note": "float32 inputs: algorithmic 6*B*BK*D FLOP per step against the cuBLAS TF32 "
+                                         "peak measured in this process (8192^3 matmul, allow_tf32, best of >= 0.4 s); "
+                                         "the path itself runs 3 fp16 planes on the kind::f16 tensor pipe"})
+    if sustained is not None and args.dtype != "fp32":   # (the sustained peak on file is a bf16 figure)
         per_s, n_s, clk_sum = sustained
         ach_s = flop_alg / per_s / 1e12
         line["roofline_sustained"] = {"bound": "tensor", "achieved": ach_s, "peak": pk["bf16_sustained"],
