@@ -118,9 +118,15 @@ int milnce_shard_combine(const float *gathered, int W, int b, float *den, float 
                          void *stream);
 /* The same, with the W packs read where they are: packs[r] = rank r's (2b + B) floats as mapped into this
  * process (host array of W device pointers), e.g. in peer-mapped memory after the caller's cross-rank
- * barrier - the all-gather of the statistics is then not needed.  W <= 16 for both variants. */
+ * barrier - the all-gather of the statistics is then not needed.  W <= 16 for both variants.
+ * scratch: NULL (one block walks all samples), or a 256-byte aligned device buffer of
+ * milnce_shard_combine_scratch_bytes(W, b) bytes whose first 4 bytes are zero before the first call (the kernel
+ * leaves them zero): the kernel then runs one sample per thread over several blocks, so that all remote loads are
+ * one round trip, and the last block to finish adds the blocks' loss sums in block order (deterministic).
+ * One scratch buffer per concurrently running call. */
+size_t milnce_shard_combine_scratch_bytes(int W, int b);
 int milnce_shard_combine_peers(const void *const *packs, int W, int b, float *den, float *nom, float *loss,
-                               void *stream);
+                               void *scratch, void *stream);
 /* Rows-only sharding WITHOUT an embedding collective.  Every rank publishes its bfloat16 shard in a buffer
  * that its peers can read directly (peer-mapped memory, e.g. torch symmetric memory: slot pointers of all
  * ranks are exchanged once at set-up), and stages the fp16 operands of all W ranks straight from the

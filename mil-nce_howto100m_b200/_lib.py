@@ -106,7 +106,9 @@ def _declare(lib):
     lib.milnce_peer_reduce_dtext.restype = i32
     lib.milnce_peer_reduce_dtext.argtypes = [c.POINTER(c.c_void_p), i32, i32, i32, i32, i32, vp, i32, vp]
     lib.milnce_shard_combine_peers.restype = i32
-    lib.milnce_shard_combine_peers.argtypes = [c.POINTER(c.c_void_p), i32, i32, fp, fp, fp, vp]
+    lib.milnce_shard_combine_peers.argtypes = [c.POINTER(c.c_void_p), i32, i32, fp, fp, fp, vp, vp]
+    lib.milnce_shard_combine_scratch_bytes.restype = sz
+    lib.milnce_shard_combine_scratch_bytes.argtypes = [i32, i32]
     lib.milnce_shard_combine.restype = i32
     lib.milnce_shard_combine.argtypes = [fp, i32, i32, fp, fp, fp, vp]
     lib.milnce_backward_shard.restype = i32

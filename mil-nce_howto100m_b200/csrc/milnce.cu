@@ -416,7 +416,7 @@ struct PeerSlots {
 // one warp per local sample i: copies video[i] and its K candidates into the slot, accumulates the local
 // |x|max of both tensors into the slot header (atomicMax on float bits; the header is zeroed by the host
 // before the launch) and produces nom_i = log sum_k exp(<video_i, text_{iK+k}>) from fp32 FMAs (loss.py:13-15).
-__global__ void __launch_bounds__(256, 8)
+__global__ void __launch_bounds__(256, 4)
 peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16 *__restrict__ text, int b, int K,
                     int D, uint8_t *__restrict__ slot, float *__restrict__ nom_own) {
     const int lane = threadIdx.x & 31;
@@ -443,32 +443,49 @@ peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16
         }
     };
     const int dv = D / 8;
+    // candidates are taken KB at a time with all their loads issued before the first use: a warp that walked
+    // the K rows one after the other paid one memory round trip per candidate (30 us for 2048 samples)
+    constexpr int KB = 4;
     for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < b; i += gridDim.x * wpb) {
         const uint4 *vrow = reinterpret_cast<const uint4 *>(video + (size_t)i * D);
         float pm = -INFINITY, ps = 0.f;
-        for (int k = 0; k < K; ++k) {
-            const uint4 *trow = reinterpret_cast<const uint4 *>(text + ((size_t)i * K + k) * D);
-            float acc = 0.f;
+        for (int k0 = 0; k0 < K; k0 += KB) {
+            float acc[KB];
+#pragma unroll
+            for (int u = 0; u < KB; ++u) acc[u] = 0.f;
             for (int c = lane; c < dv; c += 32) {
-                const uint4 qv = __ldg(vrow + c), qt = __ldg(trow + c);
-                float fv[8], ft[8];
+                const uint4 qv = __ldg(vrow + c);
+                uint4 qt[KB];
+#pragma unroll
+                for (int u = 0; u < KB; ++u)
+                    if (k0 + u < K) qt[u] = __ldg(reinterpret_cast<const uint4 *>(text + ((size_t)i * K + k0 + u) * D) + c);
+                float fv[8];
                 unpack8(qv, fv);
-                unpack8(qt, ft);
-                if (k == 0) {
+                if (k0 == 0) {
                     mv = amax8(mv, fv);
                     sv[(size_t)i * dv + c] = qv;
                 }
-                mt = amax8(mt, ft);
-                stx[((size_t)i * K + k) * dv + c] = qt;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc = fmaf(fv[j], ft[j], acc);
+                for (int u = 0; u < KB; ++u) {
+                    if (k0 + u >= K) break;
+                    float ft[8];
+                    unpack8(qt[u], ft);
+                    mt = amax8(mt, ft);
+                    stx[((size_t)i * K + k0 + u) * dv + c] = qt[u];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[u] = fmaf(fv[j], ft[j], acc[u]);
+                }
             }
-            acc = warp_sum(acc);
-            if (acc > pm) {
-                ps = ps * expf(pm - acc) + 1.f;
-                pm = acc;
-            } else {
-                ps += expf(acc - pm);
+#pragma unroll
+            for (int u = 0; u < KB; ++u) {
+                if (k0 + u >= K) break;
+                const float a = warp_sum(acc[u]);
+                if (a > pm) {
+                    ps = ps * expf(pm - a) + 1.f;
+                    pm = a;
+                } else {
+                    ps += expf(a - pm);
+                }
             }
         }
         if (lane == 0) nom_own[i] = pm + logf(ps);
@@ -490,7 +507,7 @@ peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16
 // read the peers at 95 GB/s.)
 __global__ void __launch_bounds__(256)
 stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *__restrict__ vk,
-                   __half *__restrict__ tk, Scalars *scal) {
+                   __half *__restrict__ tk, Scalars *scal, int r_lo, int r_hi, int with_video) {
     unsigned int av = 0, at = 0;
     for (int r = 0; r < W; ++r) {
         const unsigned int *h = reinterpret_cast<const unsigned int *>(ps.slot[r]);
@@ -498,7 +515,7 @@ stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *_
         at = max(at, __ldcg(h + 1));
     }
     const float s_v = pow2_scale(av), s_t = pow2_scale(at);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && with_video) {   // (the launch that stages the video publishes the scales)
         scal->absmax_bits[0] = av;
         scal->absmax_bits[1] = at;
         scal->s_video = s_v;
@@ -506,7 +523,9 @@ stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *_
         scal->inv_ss = (1.f / s_v) * (1.f / s_t);
     }
     const size_t gv = (size_t)b * D / 8, gt = gv * K;      // granules (8 elements) per shard: video, text
-    const size_t n_text = gt * W, total = n_text + gv;     // [text of rank 0 .. W-1 | own video]
+    // this launch covers [text of ranks r_lo .. r_hi-1 | own video if with_video]
+    const size_t n_text = gt * (size_t)(r_hi - r_lo), total = n_text + (with_video ? gv : 0);
+    const size_t t_off = gt * (size_t)r_lo;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     auto convert = [&](size_t g, const uint4 &q) {
         const bool is_v = g >= n_text;
@@ -516,14 +535,14 @@ stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *_
 #pragma unroll
         for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(__bfloat162float(e[j]) * sc);
         uint4 *dst = is_v ? reinterpret_cast<uint4 *>(vk) + (size_t)rank * gv + (g - n_text)
-                          : reinterpret_cast<uint4 *>(tk) + g;
+                          : reinterpret_cast<uint4 *>(tk) + t_off + g;
         *dst = *reinterpret_cast<uint4 *>(hv);
     };
     auto src = [&](size_t g) -> const uint4 * {
         // (L2-only loads: another GPU wrote this buffer since the last time this SM may have read it)
         if (g >= n_text) return reinterpret_cast<const uint4 *>(ps.slot[rank] + PEER_HEADER) + (g - n_text);
         const int r = (int)(g / gt);
-        return reinterpret_cast<const uint4 *>(ps.slot[r] + PEER_HEADER) + gv + (g - (size_t)r * gt);
+        return reinterpret_cast<const uint4 *>(ps.slot[r_lo + r] + PEER_HEADER) + gv + (g - (size_t)r * gt);
     };
     size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     for (; g + 7 * stride < total; g += 8 * stride) {
@@ -735,75 +754,69 @@ __global__ void finalize_kernel(const T *__restrict__ video, const T *__restrict
 // all-gathered array or W separate buffers in the ranks' peer-readable memory.  One block:
 //   den_j = logaddexp(row_j, logsumexp_r col_part[r][j]), nom_all, loss = mean(den - nom)
 // (replaces a cat / logsumexp / logaddexp / mean chain of eight small torch launches).
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(512)
 shard_combine_kernel(PeerSlots packs, int W, int b, int B, float *__restrict__ den,
-                     float *__restrict__ nom_all, float *__restrict__ loss) {
-    __shared__ double sh[32];
+                     float *__restrict__ nom_all, float *__restrict__ loss, unsigned int *ticket,
+                     double *__restrict__ block_sums) {
+    __shared__ double sh[16];
+    __shared__ bool last;
     double acc = 0.0;
-    // four samples per thread and round: all their loads (2 + W each, possibly from other GPUs' memory) are in
-    // flight together - one sample at a time cost a remote round trip per sample (31 us at B = 8192, W = 2)
-    constexpr int J = 4;
-    for (int j0 = threadIdx.x; j0 < B; j0 += J * blockDim.x) {
-        float row[J], nm[J], m[J], sum[J];
+    // one sample per thread when the caller gave scratch for a multi-block launch (all 2 + W loads of a sample,
+    // possibly from other GPUs' memory, in flight at once: one remote round trip for the whole kernel);
+    // otherwise a single block strides over the samples
+    constexpr int WB = 8;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < B; j += gridDim.x * blockDim.x) {
+        const int r = j / b, i = j - r * b;
+        const float *own = reinterpret_cast<const float *>(packs.slot[r]);
+        const float row = __ldcg(own + i);
+        const float nm = __ldcg(own + b + i);
+        float m = -INFINITY, sum = 0.f;
+        for (int w0 = 0; w0 < W; w0 += WB) {
+            float cp[WB];
 #pragma unroll
-        for (int u = 0; u < J; ++u) {
-            const int j = j0 + u * blockDim.x;
-            row[u] = nm[u] = -INFINITY;
-            if (j < B) {
-                const int r = j / b, i = j - r * b;
-                const float *own = reinterpret_cast<const float *>(packs.slot[r]);
-                row[u] = __ldcg(own + i);
-                nm[u] = __ldcg(own + b + i);
-            }
-            m[u] = row[u];
-            sum[u] = 0.f;
-        }
-        // column partials: running (max, sum) pairs, W loads per sample issued back to back
-        for (int w0 = 0; w0 < W; w0 += 4) {
-            float cp[J][4];
+            for (int k = 0; k < WB; ++k)
+                cp[k] = (w0 + k < W) ? __ldcg(reinterpret_cast<const float *>(packs.slot[w0 + k]) + 2 * b + j) : -INFINITY;
+            float mx = m;
 #pragma unroll
-            for (int u = 0; u < J; ++u) {
-                const int j = j0 + u * blockDim.x;
+            for (int k = 0; k < WB; ++k) mx = fmaxf(mx, cp[k]);
+            if (mx > -INFINITY) {
+                float sacc = sum * expf(m - mx);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    cp[u][k] = (j < B && w0 + k < W)
-                                   ? __ldcg(reinterpret_cast<const float *>(packs.slot[w0 + k]) + 2 * b + j)
-                                   : -INFINITY;
-            }
-#pragma unroll
-            for (int u = 0; u < J; ++u) {
-                float mx = m[u];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) mx = fmaxf(mx, cp[u][k]);
-                if (mx > -INFINITY) {
-                    float sacc = sum[u] * expf(m[u] - mx);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) sacc += expf(cp[u][k] - mx);   // exp(-inf) = 0 for the padding
-                    sum[u] = sacc;
-                    m[u] = mx;
-                }
+                for (int k = 0; k < WB; ++k) sacc += expf(cp[k] - mx);   // exp(-inf) = 0 for the padding
+                sum = sacc;
+                m = mx;
             }
         }
-#pragma unroll
-        for (int u = 0; u < J; ++u) {
-            const int j = j0 + u * blockDim.x;
-            if (j >= B) continue;
-            // the row statistic joins last: den = logaddexp(row, logsumexp_r col_part[r])
-            float s_all = sum[u], mm = m[u];
-            if (mm > -INFINITY) s_all += expf(row[u] - mm);
-            const float d = mm > -INFINITY ? mm + logf(s_all) : -INFINITY;
-            den[j] = d;
-            nom_all[j] = nm[u];
-            acc += (double)(d - nm[u]);
-        }
+        // the row statistic joins last: den = logaddexp(row, logsumexp_r col_part[r])
+        const float mm = fmaxf(m, row);
+        float d = -INFINITY;
+        if (mm > -INFINITY) d = mm + logf(sum * expf(m - mm) + expf(row - mm));
+        den[j] = d;
+        nom_all[j] = nm;
+        acc += (double)(d - nm);
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        acc = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0;
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (threadIdx.x == 0) loss[0] = (float)(acc / (double)B);
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sh[w];     // fixed order
+        if (gridDim.x == 1) {
+            loss[0] = (float)(t / (double)B);
+            last = false;
+        } else {
+            block_sums[blockIdx.x] = t;
+            __threadfence();
+            last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+        }
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        double t = 0.0;
+        for (int k = 0; k < (int)gridDim.x; ++k) t += *reinterpret_cast<volatile double *>(block_sums + k);   // block order
+        loss[0] = (float)(t / (double)B);
+        *ticket = 0;        // ready for the next call
     }
 }
 
@@ -1501,7 +1514,14 @@ extern "C" int milnce_forward_shard_peers(const void *const *slots, int W, int B
     PeerSlots ps;
     for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)slots[r < W ? r : 0];
     __half *vk = reinterpret_cast<__half *>(ws + p.off_vk), *tk = reinterpret_cast<__half *>(ws + p.off_tk);
-    stage_peers_kernel<<<4 * num_sms(), 256, 0, st>>>(ps, W, i0 / b, b, K, D, vk, tk, sc);   // ld_vk == ld_tk == D (D % 8 == 0)
+    const int rank = i0 / b;
+    const int grid = 4 * num_sms();
+    // (ld_vk == ld_tk == D since D % 8 == 0)
+    // (Tried: staging the own shard first and overlapping the other ranks' copies, on a side stream, with the
+    // similarity pass over the own column block.  The copy kernel did not get onto the SMs next to the
+    // one-CTA-per-SM GEMM, whichever was enqueued first and with 128-thread copy blocks, so the phases ran back
+    // to back with two extra launches: 209-214 us against 173 us for this form at W = 2.)
+    stage_peers_kernel<<<grid, 256, 0, st>>>(ps, W, rank, b, K, D, vk, tk, sc, 0, W, 1);
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_forward_shard_peers staging");
     return forward_shard_tail(p, row_lse, col_part, ws, st);
@@ -1582,15 +1602,20 @@ extern "C" int milnce_shard_combine(const float *gathered, int W, int b, float *
     PeerSlots ps;
     for (int r = 0; r < PEER_MAX; ++r)
         ps.slot[r] = reinterpret_cast<const uint8_t *>(gathered + (size_t)(r < W ? r : 0) * ((size_t)2 * b + (size_t)W * b));
-    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(ps, W, b, W * b, den, nom, loss);
+    shard_combine_kernel<<<1, 512, 0, (cudaStream_t)stream>>>(ps, W, b, W * b, den, nom, loss, nullptr, nullptr);
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_shard_combine");
     return 0;
 }
 
+extern "C" size_t milnce_shard_combine_scratch_bytes(int W, int b) {
+    if (W <= 0 || b <= 0) return 0;
+    return 256 + 8 * (((size_t)W * b + 511) / 512);
+}
+
 extern "C" int milnce_shard_combine_peers(const void *const *packs, int W, int b, float *den, float *nom, float *loss,
-                                          void *stream) {
-    if (!packs || !den || !nom || !loss || W <= 0 || W > PEER_MAX || b <= 0) {
+                                          void *scratch, void *stream) {
+    if (!packs || !den || !nom || !loss || W <= 0 || W > PEER_MAX || b <= 0 || (((uintptr_t)scratch) & 255)) {
         b200::set_error("milnce_shard_combine_peers: bad argument (1 <= W <= %d ranks)", PEER_MAX);
         return B200HEAD_ERR_ARG;
     }
@@ -1603,7 +1628,11 @@ extern "C" int milnce_shard_combine_peers(const void *const *packs, int W, int b
     if (rc) return rc;
     PeerSlots ps;
     for (int r = 0; r < PEER_MAX; ++r) ps.slot[r] = (const uint8_t *)packs[r < W ? r : 0];
-    shard_combine_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(ps, W, b, W * b, den, nom, loss);
+    const int B = W * b;
+    const int blocks = scratch ? (B + 511) / 512 : 1;
+    shard_combine_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(
+        ps, W, b, B, den, nom, loss, reinterpret_cast<unsigned int *>(scratch),
+        scratch ? reinterpret_cast<double *>(reinterpret_cast<uint8_t *>(scratch) + 256) : nullptr);
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_shard_combine_peers");
     return 0;

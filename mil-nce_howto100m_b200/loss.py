@@ -105,7 +105,7 @@ class CudaBackend:
         return pack, ws
 
     @staticmethod
-    def forward_shard_peers(ring, video_local, text_local, world, rank):
+    def forward_shard_peers(ring, video_local, text_local, world, rank, mark=None):
         """The rows-only forward without an embedding collective (see PeerRing in utils.py and
         include/b200head.h, milnce_forward_shard_peers).  Returns (pack, ws) like forward_shard."""
         lib = _lib.load()
@@ -117,13 +117,17 @@ class CudaBackend:
         nbytes = lib.milnce_workspace_bytes(B, K, D, _lib.BF16, b)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         pack = ring.pack        # this rank's statistics, where the peers can read them
+        mark = mark or (lambda name: None)
         slot_ptr, peer_ptrs = ring.next_slot()
+        mark("barrier_slot_free")
         with torch.cuda.device(dev):
             st = _lib.stream_ptr(dev)
             rc = lib.milnce_peer_publish(_ptr(video_local), _ptr(text_local), b, K, D, ctypes.c_void_p(slot_ptr),
                                          ctypes.c_void_p(pack.data_ptr() + 4 * b), st)
             _lib.check(rc, "milnce_peer_publish")
+            mark("publish")
             ring.barrier()      # every rank's slot is complete (and nobody still reads the slot written next step)
+            mark("barrier_published")
             arr = (ctypes.c_void_p * world)(*peer_ptrs)
             rc = lib.milnce_forward_shard_peers(arr, world, B, K, D, i0, b, ctypes.c_void_p(pack.data_ptr() - 4 * i0),
                                                 ctypes.c_void_p(pack.data_ptr() + 8 * b), _ptr(ws), nbytes, st)
@@ -178,7 +182,8 @@ class CudaBackend:
         loss = torch.empty(1, dtype=torch.float32, device=dev)
         arr = (ctypes.c_void_p * world)(*ring.pack_ptrs)
         with torch.cuda.device(dev):
-            rc = lib.milnce_shard_combine_peers(arr, world, b, _ptr(den), _ptr(nom), _ptr(loss), _lib.stream_ptr(dev))
+            rc = lib.milnce_shard_combine_peers(arr, world, b, _ptr(den), _ptr(nom), _ptr(loss), _ptr(ring.combine_scratch),
+                                                _lib.stream_ptr(dev))
         _lib.check(rc, "milnce_shard_combine_peers")
         return den, nom, loss.reshape(())
 

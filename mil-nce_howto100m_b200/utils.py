@@ -110,6 +110,8 @@ class PeerRing:
         self.rank = int(self.hdl.rank)
         self.shape = (b, K, D)
         self.side = torch.cuda.Stream(device=device)     # barrier + gradient reduction run here, beside dvideo
+        self.combine_scratch = torch.zeros(int(lib.milnce_shard_combine_scratch_bytes(world, b)), dtype=torch.uint8,
+                                           device=device)
 
     def next_slot(self):
         self.hdl.barrier(channel=0)          # nobody is still reading the slots of the previous step
@@ -195,9 +197,10 @@ class _GatheredMILNCERows(torch.autograd.Function):
         ring = opts.get("ring")
         if ring is not None:
             # no embedding collective: publish the shard, meet, stage all shards from the peers' memory
-            pack, ws = backend.forward_shard_peers(ring, v, t, world, rank)
+            pack, ws = backend.forward_shard_peers(ring, v, t, world, rank,
+                                                   mark=(lambda name: _mark(marks, name, v.device)) if marks is not None else None)
             V, T = v, t                      # (only their shapes are used from here on)
-            _mark(marks, "publish+stage+forward_kernels", v.device)
+            _mark(marks, "stage+forward_kernels", v.device)
             if opts.get("reduce") != "nccl":
                 # the statistics stay where they are: barrier, then every rank reads all W packs
                 ring.barrier()
@@ -232,7 +235,12 @@ class _GatheredMILNCERows(torch.autograd.Function):
         # default: partials in the embeddings' own 16-bit dtype - the result is rounded to that dtype anyway, and
         # a float32 payload (67 MB at B=8192) made the reduce-scatter the longest phase of the step
         # (profiles/r2_multi_timeline_*.txt); float32 on request (partial_dtype=torch.float32)
-        pdt = pdt if pdt is not None else (torch.bfloat16 if tdt == torch.bfloat16 else torch.float32)
+        # (NCCL adds 16-bit partials in 16 bits: beyond two ranks the rounding of every ring step accumulates -
+        # 1.5e-2 on dtext at eight ranks, harness/config5.py - so the collective then carries float32; the peer
+        # path sums bf16 partials in float32 and keeps the 16-bit payload at any rank count)
+        if pdt is None:
+            two_byte = tdt == torch.bfloat16 and ((ring is not None and reduce != "nccl") or dims[0] // b <= 2)
+            pdt = torch.bfloat16 if two_byte else torch.float32
         # the text-gradient partial first, so that its reduce-scatter runs while dvideo is computed
         if ring is not None and pdt == torch.bfloat16 and reduce != "nccl":
             world, rank = dims[0] // b, i0 // b

@@ -156,6 +156,45 @@ def main():
     lines.append(f"  all-gather of the statistics ({small.numel() * 4 / 1e3:.0f} KB per rank)                {time_coll(lambda: dist.all_gather_into_tensor(small_all, small)):8.0f}")
     lines.append(f"  reduce-scatter dtext partial float32 ({p32.numel() * 4 / 1e6:.0f} MB in)              {time_coll(lambda: dist.reduce_scatter_tensor(o32, p32)):8.0f}")
     lines.append(f"  reduce-scatter dtext partial bfloat16 ({p16.numel() * 2 / 1e6:.0f} MB in)             {time_coll(lambda: dist.reduce_scatter_tensor(o16, p16)):8.0f}")
+    # the peer-memory kernels alone (GPU time without host gaps: 20 back-to-back launches between two events)
+    try:
+        import ctypes
+        from milnce_b200 import _lib
+        from milnce_b200.utils import PeerRing
+        lib = _lib.load()
+        ring = PeerRing(b, K, D, dev)
+        st = _lib.stream_ptr(dev)
+        P = lambda x: ctypes.c_void_p(x.data_ptr())
+        nom = torch.empty(b, device=dev)
+        nbytes = lib.milnce_workspace_bytes(B, K, D, _lib.BF16, b)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        row = torch.empty(B, device=dev)
+        slots = (ctypes.c_void_p * world)(*ring.ptrs)
+        packs = (ctypes.c_void_p * world)(*ring.pack_ptrs)
+        grads = (ctypes.c_void_p * world)(*ring.grad_ptrs)
+        den, nm, ls = torch.empty(B, device=dev), torch.empty(B, device=dev), torch.empty(1, device=dev)
+        dt16 = torch.empty(b * K, D, dtype=torch.bfloat16, device=dev)
+        pub = lambda: lib.milnce_peer_publish(P(vd), P(td), b, K, D, ctypes.c_void_p(ring.ptrs[rank]), P(nom), st)
+        pub()
+        ring.barrier()
+        fwd = lambda: lib.milnce_forward_shard_peers(slots, world, B, K, D, rank * b, b,
+                                                     ctypes.c_void_p(row.data_ptr()), ctypes.c_void_p(ring.pack.data_ptr() + 8 * b),
+                                                     P(ws), nbytes, st)
+        assert fwd() == 0
+        ring.barrier()
+        lines.append("\n## peer-memory kernels alone (GPU time, 20 back-to-back launches; us)")
+        lines.append(f"  symmetric-memory barrier                                      {time_coll(ring.barrier):8.0f}")
+        lines.append(f"  milnce_peer_publish (header memset + copy of the shard + nom)   {time_coll(pub):8.0f}")
+        lines.append(f"  milnce_forward_shard_peers (stage from W slots + similarity pass + merges) {time_coll(fwd):8.0f}")
+        loc = torch.empty(B * K * D + B * D, dtype=torch.bfloat16, device=dev)
+        lines.append(f"  milnce_shard_combine_peers                                    "
+                     f"{time_coll(lambda: lib.milnce_shard_combine_peers(packs, world, b, P(den), P(nm), P(ls), P(ring.combine_scratch), st)):8.0f}")
+        lines.append(f"  milnce_peer_reduce_dtext ({(world - 1) * b * K * D * 2 / 1e6:.0f} MB from the peers)               "
+                     f"{time_coll(lambda: lib.milnce_peer_reduce_dtext(grads, world, rank, b, K, D, P(dt16), _lib.BF16, st)):8.0f}")
+        ring.barrier()
+        torch.cuda.synchronize()
+    except Exception as e:      # symmetric memory unavailable: keep the rest of the record
+        lines.append(f"\n## peer-memory kernels alone: skipped ({type(e).__name__}: {e})")
     if rank == 0:
         text = "\n".join(lines) + "\n"
         print(text)

@@ -19,7 +19,7 @@ def _p(t):
     return ctypes.c_void_p(t.data_ptr())
 
 
-@pytest.mark.parametrize("W,b,K,D", [(2, 64, 4, 512), (4, 64, 2, 72), (3, 128, 1, 256)])
+@pytest.mark.parametrize("W,b,K,D", [(2, 64, 4, 512), (4, 64, 2, 72), (3, 128, 1, 256), (4, 128, 2, 64), (3, 256, 4, 128)])
 def test_peer_forward_and_reduce_match_the_gathered_path(W, b, K, D):
     lib = _lib.load()
     B = W * b
@@ -49,8 +49,17 @@ def test_peer_forward_and_reduce_match_the_gathered_path(W, b, K, D):
     # the same from W separate buffers (what the ranks' peer-readable statistics packs are)
     den2, nom2, loss2 = torch.empty_like(den), torch.empty_like(nom), torch.empty(1, device="cuda")
     karr = (ctypes.c_void_p * W)(*[x.data_ptr() for x in packs])
-    _lib.check(lib.milnce_shard_combine_peers(karr, W, b, _p(den2), _p(nom2), _p(loss2), st), "combine_peers")
+    _lib.check(lib.milnce_shard_combine_peers(karr, W, b, _p(den2), _p(nom2), _p(loss2), None, st), "combine_peers")
     assert torch.equal(den, den2) and torch.equal(nom, nom2) and loss.item() == loss2.item()
+    # multi-block form (scratch given): same den / nom, loss equal up to the order of the double additions, and
+    # the scratch ticket is left at zero so that the call can be repeated
+    scratch = torch.zeros(lib.milnce_shard_combine_scratch_bytes(W, b), dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        den3, nom3, loss3 = torch.empty_like(den), torch.empty_like(nom), torch.empty(1, device="cuda")
+        _lib.check(lib.milnce_shard_combine_peers(karr, W, b, _p(den3), _p(nom3), _p(loss3), _p(scratch), st), "combine_peers")
+        assert torch.equal(den, den3) and torch.equal(nom, nom3)
+        assert abs(loss.item() - loss3.item()) <= 1e-6 * abs(loss.item())
+    assert int(scratch[:4].view(torch.int32)[0]) == 0
     ref_loss, ref_dv, ref_dt, ref_den, ref_nom = milnce_oracle.milnce_closed_form(V.float().cpu().double().numpy(),
                                                                                 T.float().cpu().double().numpy(), 1.0)
     assert abs(loss.item() - ref_loss) <= 1e-5 * abs(ref_loss)
