@@ -505,17 +505,36 @@ peer_publish_kernel(const __nv_bfloat16 *__restrict__ video, const __nv_bfloat16
 // both tensors are flat arrays: a grid-stride loop over 16-byte granules, eight independent loads in flight
 // per thread, 512 contiguous bytes per warp instruction.  (A 64 x 64-tile version with two loads per thread
 // read the peers at 95 GB/s.)
+// The sources are visited in ROTATED order - rank r reads the text of ranks r, r+1, ..., r+W-1 (mod W) - because
+// all ranks run this kernel at the same moment: in natural order every rank pulled from rank 0 first, then from
+// rank 1, ..., and one GPU's egress served all readers at once (29 MB in ~220 us at W = 8, half the rate of W = 2).
 __global__ void __launch_bounds__(256)
 stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *__restrict__ vk,
-                   __half *__restrict__ tk, Scalars *scal, int r_lo, int r_hi, int with_video) {
-    unsigned int av = 0, at = 0;
-    for (int r = 0; r < W; ++r) {
-        const unsigned int *h = reinterpret_cast<const unsigned int *>(ps.slot[r]);
-        av = max(av, __ldcg(h));          // positive floats compare like their bit patterns
-        at = max(at, __ldcg(h + 1));
+                   __half *__restrict__ tk, Scalars *scal) {
+    // The slot headers are read by ONE warp per block (lane r reads rank r's) and handed on through shared
+    // memory.  When every thread read them, each GPU's two header words were hit by ~9 000 warp requests per
+    // reader over NVLink, all on one L2 sector: the kernel's time grew by ~30 us per remote rank (218 us at W = 8).
+    __shared__ unsigned int s_abs[2];
+    if (threadIdx.x < 32) {
+        unsigned int hv = 0, ht = 0;
+        if ((int)threadIdx.x < W) {
+            const unsigned int *h = reinterpret_cast<const unsigned int *>(ps.slot[threadIdx.x]);
+            hv = __ldcg(h);               // positive floats compare like their bit patterns
+            ht = __ldcg(h + 1);
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            hv = max(hv, __shfl_xor_sync(0xffffffffu, hv, o));
+            ht = max(ht, __shfl_xor_sync(0xffffffffu, ht, o));
+        }
+        if (threadIdx.x == 0) {
+            s_abs[0] = hv;
+            s_abs[1] = ht;
+        }
     }
+    __syncthreads();
+    const unsigned int av = s_abs[0], at = s_abs[1];
     const float s_v = pow2_scale(av), s_t = pow2_scale(at);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && with_video) {   // (the launch that stages the video publishes the scales)
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         scal->absmax_bits[0] = av;
         scal->absmax_bits[1] = at;
         scal->s_video = s_v;
@@ -523,10 +542,14 @@ stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *_
         scal->inv_ss = (1.f / s_v) * (1.f / s_t);
     }
     const size_t gv = (size_t)b * D / 8, gt = gv * K;      // granules (8 elements) per shard: video, text
-    // this launch covers [text of ranks r_lo .. r_hi-1 | own video if with_video]
-    const size_t n_text = gt * (size_t)(r_hi - r_lo), total = n_text + (with_video ? gv : 0);
-    const size_t t_off = gt * (size_t)r_lo;
+    const size_t n_text = gt * W, total = n_text + gv;     // [text of ranks rank, rank+1, ... (mod W) | own video]
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    auto source = [&](size_t g, int &r, size_t &o) {       // text granule g -> (source rank, granule within its text)
+        const int p = (int)(g / gt);
+        o = g - (size_t)p * gt;
+        r = rank + p;
+        if (r >= W) r -= W;
+    };
     auto convert = [&](size_t g, const uint4 &q) {
         const bool is_v = g >= n_text;
         const float sc = is_v ? s_v : s_t;
@@ -534,15 +557,24 @@ stage_peers_kernel(PeerSlots ps, int W, int rank, int b, int K, int D, __half *_
         __align__(16) __half hv[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) hv[j] = __float2half_rn(__bfloat162float(e[j]) * sc);
-        uint4 *dst = is_v ? reinterpret_cast<uint4 *>(vk) + (size_t)rank * gv + (g - n_text)
-                          : reinterpret_cast<uint4 *>(tk) + t_off + g;
+        uint4 *dst;
+        if (is_v) {
+            dst = reinterpret_cast<uint4 *>(vk) + (size_t)rank * gv + (g - n_text);
+        } else {
+            int r;
+            size_t o;
+            source(g, r, o);
+            dst = reinterpret_cast<uint4 *>(tk) + (size_t)r * gt + o;
+        }
         *dst = *reinterpret_cast<uint4 *>(hv);
     };
     auto src = [&](size_t g) -> const uint4 * {
         // (L2-only loads: another GPU wrote this buffer since the last time this SM may have read it)
         if (g >= n_text) return reinterpret_cast<const uint4 *>(ps.slot[rank] + PEER_HEADER) + (g - n_text);
-        const int r = (int)(g / gt);
-        return reinterpret_cast<const uint4 *>(ps.slot[r_lo + r] + PEER_HEADER) + gv + (g - (size_t)r * gt);
+        int r;
+        size_t o;
+        source(g, r, o);
+        return reinterpret_cast<const uint4 *>(ps.slot[r] + PEER_HEADER) + gv + o;
     };
     size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     for (; g + 7 * stride < total; g += 8 * stride) {
@@ -1521,7 +1553,7 @@ extern "C" int milnce_forward_shard_peers(const void *const *slots, int W, int B
     // similarity pass over the own column block.  The copy kernel did not get onto the SMs next to the
     // one-CTA-per-SM GEMM, whichever was enqueued first and with 128-thread copy blocks, so the phases ran back
     // to back with two extra launches: 209-214 us against 173 us for this form at W = 2.)
-    stage_peers_kernel<<<grid, 256, 0, st>>>(ps, W, rank, b, K, D, vk, tk, sc, 0, W, 1);
+    stage_peers_kernel<<<grid, 256, 0, st>>>(ps, W, rank, b, K, D, vk, tk, sc);
     b200::note_launches(1);
     B200_LAUNCH_OK("milnce_forward_shard_peers staging");
     return forward_shard_tail(p, row_lse, col_part, ws, st);
