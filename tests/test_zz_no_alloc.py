@@ -117,3 +117,27 @@ def test_noalloc_rejects_sizes_beyond_the_builtin_buffer():
     assert rc == -4
     msg = lib.b200head_last_error().decode()
     assert "needs" in msg and "sdtw_forward" in msg
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_noalloc_uses_the_scratch_of_the_current_device():
+    """The built-in buffer exists once per GPU and its address is looked up per device: a call on the second GPU
+    after one on the first must use the second GPU's own copy (a cached pointer of device 0 would fault there or
+    give wrong numbers)."""
+    lib = milnce_b200._lib.load()
+    g = torch.Generator().manual_seed(99)
+    xs = torch.randn(7, 48, 16, generator=g)
+    ys = torch.randn(7, 50, 16, generator=g)
+    outs = []
+    for dev in (0, 1, 0):
+        with torch.cuda.device(dev):
+            x, y = xs.cuda(dev), ys.cuda(dev)
+            out = torch.full((7,), float("nan"), device=f"cuda:{dev}")
+            rc = lib.sdtw_forward_noalloc(_ptr(x), _ptr(y), 7, 48, 50, 16, ctypes.c_float(0.5), ctypes.c_float(0.0),
+                                          KINDS["euclidean"], _ptr(None), _ptr(out),
+                                          milnce_b200._lib.stream_ptr(torch.device("cuda", dev)))
+            milnce_b200._lib.check(rc, "sdtw_forward_noalloc")
+            torch.cuda.synchronize(dev)
+            outs.append(out.cpu())
+    assert torch.isfinite(outs[0]).all()
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
