@@ -634,6 +634,21 @@ bwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CU
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = tl.tmem_slot;
 
+#ifdef SDTC_EARLY_PREFETCH
+    // Variant builds only (measured: 0.1165 vs 0.1135 ms per fwd+bwd without it).  HBM is idle while warps 0 and 1
+    // run the wavefront and the coefficient pass, so an otherwise idle warp asks for both sequences to be brought
+    // into L2 for the streaming phase below - but that phase already runs its own-term prefetch two items ahead,
+    // and 67 MB of early prefetches compete with the weights and the gradient stores for L2.
+    if (warp == 2) {
+        if (tc::elect_one()) {
+            const int dlim = min(d, 1024);
+            for (int c0 = 0; c0 < dlim; c0 += KC) tma_prefetch_l2_3d(&map_y, c0, 0, by);
+            for (int c0 = 0; c0 < dlim; c0 += KC) tma_prefetch_l2_3d(&map_x, c0, 0, bx);
+        }
+        __syncwarp();
+    }
+#endif
+
     // ---- 1. reverse wavefront: lane c = column j; at step p the cell (i = p - c, j = c) ----
     if (warp < 2) {
         tc::mbar_wait(&tl.wfull, 0);
