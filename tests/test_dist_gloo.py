@@ -183,3 +183,14 @@ def test_world_size_one_needs_no_process_group():
     assert abs(loss.item() - ref_loss) < 1e-12
     assert np.allclose(V.grad.numpy(), ref_dv, rtol=1e-11, atol=1e-14)
     assert np.allclose(T.grad.numpy(), ref_dt, rtol=1e-11, atol=1e-14)
+
+
+def test_option_names_are_validated():
+    sys.path.insert(0, ROOT)
+    import milnce_b200
+    for kw in ({"scheme": "columns"}, {"gather": "mpi"}, {"reduce": "ring"}):
+        with pytest.raises(ValueError):
+            milnce_b200.GatheredMILNCELoss(**kw)
+    # the documented values construct without a process group or a GPU
+    for red in ("auto", "nccl", "pull", "push"):
+        milnce_b200.GatheredMILNCELoss(gather="auto", reduce=red)
