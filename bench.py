@@ -7,9 +7,10 @@ Headline metric: MIL-NCE forward+backward similarity-pairs/s at global batch
 B=8192, K=4, D=512 (BASELINE.json configs[1]; pairs per step = B * B*K).  One
 "step" = one forward + one backward of the loss on one batch of synthetic
 embeddings.  At N > 1 GPUs the global batch is sharded over ranks (configs[3]):
-embeddings are all-gathered with NCCL and every rank computes its share of the
+every rank obtains the other ranks' text embeddings (read from their peer-mapped
+memory on one node, else an NCCL all-gather) and computes its share of the
 similarity matrix (strong scaling: total work fixed); rank 0 first checks the
-sharded loss and its gradient slices against the single-GPU module.
+sharded loss and its gradient slices against the single-GPU result.
 
 One JSON line is printed by rank 0.  Besides the contract keys it carries
   roofline            tensor-pipe roofline of the timed region; its peak is the burst or the
