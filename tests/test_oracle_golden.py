@@ -96,3 +96,37 @@ def test_sdtw_module_matches_reference(path):
             continue
         assert rel_err(dx, g[key + "_dx"]) < gtol, key
         assert rel_err(dy, g[key + "_dy"]) < gtol, key
+
+
+def test_sdtw_negative_restatement_matches_reference():
+    """The (b, L, b, L)-view form of reference loss.py:77-91 that milnce_b200.SDTW_negative uses (diagonal blocks
+    set to 0 before the exp, divisor b - 1), evaluated in float64 with the oracle's soft-DTW, against the executed
+    reference at the size it hard-codes (160 x 8 x 512)."""
+    import os
+
+    import numpy as np
+
+    from oracle import sdtw_oracle
+    f = np.load(os.path.join(os.path.dirname(__file__), "golden", "composite_losses.npz"))
+    v = f["neg_video_i8"].astype(np.float64) / 32
+    t = f["neg_text_i8"].astype(np.float64) / 32
+    b, L, d = v.shape
+    sdtw, dv_s, dt_s, _ = sdtw_oracle.softdtw(v, t, gamma=0.1, dist_func="cosine", grad_out=np.full(b, 1.0 / b))
+    pw = (v.reshape(-1, d) @ t.reshape(-1, d).T).reshape(b, L, b, L)
+    for i in range(b):
+        pw[i, :, i, :] = 0.0
+    e = np.exp(pw)
+    neg = e.sum(axis=(1, 2, 3))
+    loss = np.mean(sdtw + neg / (b - 1))
+    assert abs(loss - float(f["neg_out"])) < 1e-9 * abs(float(f["neg_out"]))
+    # gradient of the negative term: masked entries are constants
+    for i in range(b):
+        e[i, :, i, :] = 0.0
+    w = e / (b * (b - 1))
+    dv = dv_s + np.einsum("ipjq,jqd->ipd", w, t)
+    dt = dt_s + np.einsum("ipjq,ipd->jqd", w, v)
+    # (the reference's CPU soft-DTW hands its matrices back through float32, soft_dtw_cuda.py:257,270: 1e-6)
+    def rel(a, r):
+        return np.linalg.norm(a - r) / np.linalg.norm(r)
+    assert rel(dv[:2], f["neg_dvideo_first2"]) < 2e-6
+    assert rel(dt[:2], f["neg_dtext_first2"]) < 2e-6
