@@ -125,8 +125,9 @@ def test_sdtw_negative_restatement_matches_reference():
     w = e / (b * (b - 1))
     dv = dv_s + np.einsum("ipjq,jqd->ipd", w, t)
     dt = dt_s + np.einsum("ipjq,ipd->jqd", w, v)
-    # (the reference's CPU soft-DTW hands its matrices back through float32, soft_dtw_cuda.py:257,270: 1e-6)
+    # (the reference CPU soft-DTW hands R back through float32, soft_dtw_cuda.py:257, and its backward divides
+    # differences of R by gamma = 0.1: a few 1e-6 on the gradients)
     def rel(a, r):
         return np.linalg.norm(a - r) / np.linalg.norm(r)
-    assert rel(dv[:2], f["neg_dvideo_first2"]) < 2e-6
-    assert rel(dt[:2], f["neg_dtext_first2"]) < 2e-6
+    assert rel(dv[:2], f["neg_dvideo_first2"]) < 1e-5
+    assert rel(dt[:2], f["neg_dtext_first2"]) < 1e-5
