@@ -139,8 +139,8 @@ int milnce_shard_combine_peers(const void *const *packs, int W, int b, float *de
  *                            slot as mapped into THIS process), then as milnce_forward_shard:
  *                            row_lse[i0, i0+n), col_part[0, B).
  * Backward: milnce_backward_shard with reuse_forward_ws = 1 (it reads only the workspace).  The caller must
- * not let a rank overwrite its slot while a peer may still be reading it (two slots used alternately and the
- * per-step barrier are enough).  Needs b = B / W a multiple of 64, D a multiple of 8, W <= 16. */
+ * not let a rank overwrite its slot while a peer may still be reading it (a cross-rank exchange between the
+ * staging of one step and the publish of the next - e.g. the one that distributes the statistics - is enough).  Needs b = B / W a multiple of 64, D a multiple of 8, W <= 16. */
 size_t milnce_peer_slot_bytes(int b, int K, int D);
 int milnce_peer_publish(const void *video_local, const void *text_local, int b, int K, int D, void *slot,
                         float *nom_own, void *stream);

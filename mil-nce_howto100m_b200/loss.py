@@ -119,14 +119,13 @@ class CudaBackend:
         pack = ring.pack        # this rank's statistics, where the peers can read them
         mark = mark or (lambda name: None)
         slot_ptr, peer_ptrs = ring.next_slot()
-        mark("barrier_slot_free")
         with torch.cuda.device(dev):
             st = _lib.stream_ptr(dev)
             rc = lib.milnce_peer_publish(_ptr(video_local), _ptr(text_local), b, K, D, ctypes.c_void_p(slot_ptr),
                                          ctypes.c_void_p(pack.data_ptr() + 4 * b), st)
             _lib.check(rc, "milnce_peer_publish")
             mark("publish")
-            ring.barrier()      # every rank's slot is complete (and nobody still reads the slot written next step)
+            ring.barrier()      # every rank's slot is complete
             mark("barrier_published")
             arr = (ctypes.c_void_p * world)(*peer_ptrs)
             rc = lib.milnce_forward_shard_peers(arr, world, B, K, D, i0, b, ctypes.c_void_p(pack.data_ptr() - 4 * i0),

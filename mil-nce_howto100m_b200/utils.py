@@ -79,10 +79,11 @@ class PeerRing:
 
     The rows scheme can then skip the NCCL all-gather of the embeddings: every rank copies its shard into
     its slot (milnce_peer_publish), the ranks meet at a device-side barrier, and the staging kernel reads
-    all shards straight from the peers' slots over NVLink (milnce_forward_shard_peers).  One slot, two
-    barriers per step: the first keeps a fast rank from overwriting a slot that a slow peer is still
-    reading from the previous step, the second says that every slot is complete.  (Barriers are kernels on
-    the current stream, so the sequence can be captured in a CUDA graph.)
+    all shards straight from the peers' slots over NVLink (milnce_forward_shard_peers).  One slot, ONE
+    barrier before it is read ("every slot is complete").  No barrier is needed before a rank overwrites its
+    slot in the next step: it gets there only after passing that step's statistics exchange (a barrier, or an
+    all-gather), which every rank enters only after its staging kernel - the last reader of the slots - has
+    finished.  (Barriers are kernels on the current stream, so the sequence can be captured in a CUDA graph.)
 
     The same allocation holds this rank's partial text gradient: backward writes it there, a third barrier
     follows, and every rank sums its own block of all partials from the peers' memory
@@ -114,7 +115,6 @@ class PeerRing:
                                            device=device)
 
     def next_slot(self):
-        self.hdl.barrier(channel=0)          # nobody is still reading the slots of the previous step
         return self.ptrs[self.rank], list(self.ptrs)
 
     def barrier(self):
