@@ -67,6 +67,11 @@ def main():
         return
     import milnce_b200
 
+    # the JSON line must be the only thing on stdout, and NCCL prints its version banner there
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -198,8 +203,12 @@ def main():
                                   "note": "informational: the reference arm rounds its logits to bf16 under autocast"},
     }
     out["parity_ok"] = bool(ok)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
     if rank == 0:
         print(json.dumps(out), flush=True)
+    os.dup2(2, 1)
     if world > 1:
         dist.destroy_process_group()
     if not ok:
